@@ -1,0 +1,90 @@
+// Shared host-side plumbing for libb2g16: context, error reporting, device buffers.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <map>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/b2g16.h"
+#include "ec.cuh"
+#include "ntt_kernels.cuh"
+
+namespace b2 {
+
+struct NttDomain;
+
+struct Ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;      // main stream (caller-visible ordering)
+    bool own_stream = false;
+    cudaStream_t aux[4] = {nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev_fork = nullptr, ev_join[4] = {nullptr, nullptr, nullptr, nullptr};
+    std::string last_error;
+    std::mutex mu;
+    Fr* roots_fwd = nullptr;            // w_{2^11}^j, j < 1024
+    Fr* roots_inv = nullptr;
+    std::map<int, NttDomain*> domains;
+    uint64_t launches = 0;              // kernels launched by this library (bench "gpu_launches")
+};
+
+struct CudaError { cudaError_t e; const char* what; const char* file; int line; };
+
+#define B2_CUDA(expr)                                                                         \
+    do {                                                                                      \
+        cudaError_t _e = (expr);                                                              \
+        if (_e != cudaSuccess) throw ::b2::CudaError{_e, #expr, __FILE__, __LINE__};           \
+    } while (0)
+
+struct ArgError { int code; std::string msg; };
+#define B2_REQUIRE(cond, code, msg)                                   \
+    do { if (!(cond)) throw ::b2::ArgError{(code), (msg)}; } while (0)
+
+// RAII stream-ordered device buffer
+template <class T> struct DevBuf {
+    T* p = nullptr; size_t n = 0; cudaStream_t s = nullptr;
+    DevBuf() {}
+    DevBuf(size_t count, cudaStream_t st) { alloc(count, st); }
+    void alloc(size_t count, cudaStream_t st) {
+        free(); n = count; s = st;
+        if (count) B2_CUDA(cudaMallocAsync((void**)&p, count * sizeof(T), st));
+    }
+    void free() { if (p) { cudaFreeAsync(p, s); p = nullptr; n = 0; } }
+    ~DevBuf() { free(); }
+    DevBuf(const DevBuf&) = delete; DevBuf& operator=(const DevBuf&) = delete;
+    DevBuf(DevBuf&& o) noexcept : p(o.p), n(o.n), s(o.s) { o.p = nullptr; }
+    DevBuf& operator=(DevBuf&& o) noexcept { free(); p = o.p; n = o.n; s = o.s; o.p = nullptr; return *this; }
+    T* get() const { return p; }
+};
+
+inline int grid_for(size_t n, int block, int max_blocks = 148 * 16) {
+    size_t g = (n + block - 1) / block;
+    if (g > (size_t)max_blocks) g = max_blocks;
+    return g ? (int)g : 1;
+}
+
+// ---- entry points implemented across the .cu files (all operate on ctx->stream) ----
+// ingest.cu
+void fr_from_bytes_dev(Ctx* c, const uint8_t* d_bytes, Fr* d_out, size_t n, int* d_bad);     // canonical -> Montgomery
+void fr_to_bytes_dev(Ctx* c, const Fr* d_in, uint8_t* d_bytes, size_t n);                      // Montgomery -> canonical
+void g1_from_bytes_dev(Ctx* c, const uint8_t* d_bytes, G1Affine* d_out, size_t n, int* d_bad);
+void g2_from_bytes_dev(Ctx* c, const uint8_t* d_bytes, G2Affine* d_out, size_t n, int* d_bad);
+void g1_to_bytes_dev(Ctx* c, const G1Affine* d_in, uint8_t* d_bytes, size_t n);
+void g2_to_bytes_dev(Ctx* c, const G2Affine* d_in, uint8_t* d_bytes, size_t n);
+void scalars_check_dev(Ctx* c, const uint8_t* d_bytes, size_t n, int* d_bad);
+// ntt.cu
+NttDomain* ntt_domain(Ctx* c, int log_n);
+void ntt_free_domains(Ctx* c);
+void ntt_init_roots(Ctx* c);
+// natural-order in/out transform on Montgomery data (the evaluation_domain API)
+void ntt_natural(Ctx* c, Fr* d_data, int log_n, bool inverse, bool coset);
+// witness-map chain: a,b,c evaluations (natural, Montgomery; destroyed) -> H coefficients
+// written to d_h_canonical as canonical 32-byte scalars in natural order.
+void h_from_abc_dev(Ctx* c, Fr* d_a, Fr* d_b, Fr* d_c, int log_m, uint32_t* d_h_canonical);
+// msm.cu : result in XYZZ (Montgomery) written to d_out
+void msm_g1_dev(Ctx* c, const G1Affine* d_bases, const uint32_t* d_scalars_canonical, size_t n, G1Xyzz* d_out, cudaStream_t st);
+void msm_g2_dev(Ctx* c, const G2Affine* d_bases, const uint32_t* d_scalars_canonical, size_t n, G2Xyzz* d_out, cudaStream_t st);
+
+}  // namespace b2

@@ -1,0 +1,278 @@
+// Montgomery prime-field arithmetic on 32-bit limbs for sm_100a.
+//
+// Replaces what the reference delegates to crypto3-multiprecision `modular_adaptor`
+// and crypto3-algebra `fields::bls12_{base,scalar}_field<381>` (un-vendored; SURVEY.md
+// §8 a15).  Values are little-endian arrays of N uint32 limbs in Montgomery form
+// (x * 2^(32N) mod p), always fully reduced to [0, p).
+//
+// The multiplier keeps two interleaved accumulators ("even" and "odd" columns) so that
+// every 32x32->64 product is one `mad.lo.cc / madc.hi.cc` pair on a two-register
+// aligned pair -- ptxas fuses each pair into a single IMAD.WIDE(.X) on the FMA pipe.
+// Cost: 2*N^2 wide MADs + N low MULs per product (N=12: 288+12, N=8: 128+8).
+//
+// Every primitive has a host emulation (carry flag in a thread-local) so the exact
+// limb algorithm is unit-tested on the CPU (tests/test_host_emulation.py) before it
+// is run on a B200.
+#pragma once
+#include <stdint.h>
+
+#if defined(__CUDACC__)
+#define B2_HD __host__ __device__ __forceinline__
+#define B2_D __device__ __forceinline__
+#else
+#define B2_HD inline
+#define B2_D inline
+#endif
+
+#if !defined(__CUDACC__)
+struct uint4 { uint32_t x, y, z, w; };      // host-emulation builds only
+#endif
+
+namespace b2 {
+
+// ---------------------------------------------------------------- PTX primitives
+namespace ptx {
+#if defined(__CUDA_ARCH__)
+B2_D uint32_t add_cc(uint32_t a, uint32_t b) { uint32_t r; asm volatile("add.cc.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+B2_D uint32_t addc_cc(uint32_t a, uint32_t b) { uint32_t r; asm volatile("addc.cc.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+B2_D uint32_t addc(uint32_t a, uint32_t b) { uint32_t r; asm volatile("addc.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+B2_D uint32_t sub_cc(uint32_t a, uint32_t b) { uint32_t r; asm volatile("sub.cc.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+B2_D uint32_t subc_cc(uint32_t a, uint32_t b) { uint32_t r; asm volatile("subc.cc.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+B2_D uint32_t subc(uint32_t a, uint32_t b) { uint32_t r; asm volatile("subc.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+B2_D uint32_t mad_lo_cc(uint32_t a, uint32_t b, uint32_t c) { uint32_t r; asm volatile("mad.lo.cc.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
+B2_D uint32_t madc_lo_cc(uint32_t a, uint32_t b, uint32_t c) { uint32_t r; asm volatile("madc.lo.cc.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
+B2_D uint32_t madc_hi_cc(uint32_t a, uint32_t b, uint32_t c) { uint32_t r; asm volatile("madc.hi.cc.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
+B2_D uint32_t madc_hi(uint32_t a, uint32_t b, uint32_t c) { uint32_t r; asm volatile("madc.hi.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
+#else
+// Host emulation: one carry flag per thread, same semantics as PTX CC.CF.
+inline uint32_t& cf() { static thread_local uint32_t f = 0; return f; }
+inline uint32_t add_cc(uint32_t a, uint32_t b) { uint64_t t = (uint64_t)a + b; cf() = (uint32_t)(t >> 32); return (uint32_t)t; }
+inline uint32_t addc_cc(uint32_t a, uint32_t b) { uint64_t t = (uint64_t)a + b + cf(); cf() = (uint32_t)(t >> 32); return (uint32_t)t; }
+inline uint32_t addc(uint32_t a, uint32_t b) { return a + b + cf(); }
+inline uint32_t sub_cc(uint32_t a, uint32_t b) { uint64_t t = (uint64_t)a - b; cf() = (uint32_t)(t >> 32) & 1; return (uint32_t)t; }
+inline uint32_t subc_cc(uint32_t a, uint32_t b) { uint64_t t = (uint64_t)a - b - cf(); cf() = (uint32_t)(t >> 32) & 1; return (uint32_t)t; }
+inline uint32_t subc(uint32_t a, uint32_t b) { return a - b - cf(); }
+inline uint32_t mad_lo_cc(uint32_t a, uint32_t b, uint32_t c) { uint64_t t = (uint64_t)(uint32_t)((uint64_t)a * b) + c; cf() = (uint32_t)(t >> 32); return (uint32_t)t; }
+inline uint32_t madc_lo_cc(uint32_t a, uint32_t b, uint32_t c) { uint64_t t = (uint64_t)(uint32_t)((uint64_t)a * b) + c + cf(); cf() = (uint32_t)(t >> 32); return (uint32_t)t; }
+inline uint32_t madc_hi_cc(uint32_t a, uint32_t b, uint32_t c) { uint64_t t = (((uint64_t)a * b) >> 32) + c + cf(); cf() = (uint32_t)(t >> 32); return (uint32_t)t; }
+inline uint32_t madc_hi(uint32_t a, uint32_t b, uint32_t c) { return (uint32_t)((((uint64_t)a * b) >> 32) + c + cf()); }
+#endif
+}  // namespace ptx
+
+// ------------------------------------------------------------------ field params
+// All constants below are re-derived and asserted by tests/test_host_emulation.py
+// (p, r from the BLS parameter; R, R^2, -p^-1 by big-int arithmetic).
+struct FrParams {
+    static constexpr int N = 8;
+    // r = 0x73eda753299d7d483339d80809a1d80553bda402fffe5bfeffffffff00000001
+    B2_HD static constexpr uint32_t P(int i) {
+        constexpr uint32_t t[8] = {0x00000001u, 0xffffffffu, 0xfffe5bfeu, 0x53bda402u,
+                                      0x09a1d805u, 0x3339d808u, 0x299d7d48u, 0x73eda753u};
+        return t[i];
+    }
+    static constexpr uint32_t INV = 0xffffffffu;          // -r^-1 mod 2^32
+    B2_HD static constexpr uint32_t ONE(int i) {
+        constexpr uint32_t t[8] = {0xfffffffeu, 0x00000001u, 0x00034802u, 0x5884b7fau,
+                                        0xecbc4ff5u, 0x998c4fefu, 0xacc5056fu, 0x1824b159u};
+        return t[i];
+    }   // 2^256 mod r
+    B2_HD static constexpr uint32_t R2(int i) {
+        constexpr uint32_t t[8] = {0xf3f29c6du, 0xc999e990u, 0x87925c23u, 0x2b6cedcbu,
+                                       0x7254398fu, 0x05d31496u, 0x9f59ff11u, 0x0748d9d9u};
+        return t[i];
+    }    // 2^512 mod r
+};
+struct FqParams {
+    static constexpr int N = 12;
+    // p = 0x1a0111ea397fe69a4b1ba7b6434bacd764774b84f38512bf6730d2a0f6b0f6241eabfffeb153ffffb9feffffffffaaab
+    B2_HD static constexpr uint32_t P(int i) {
+        constexpr uint32_t t[12] = {0xffffaaabu, 0xb9feffffu, 0xb153ffffu, 0x1eabfffeu, 0xf6b0f624u, 0x6730d2a0u,
+                                       0xf38512bfu, 0x64774b84u, 0x434bacd7u, 0x4b1ba7b6u, 0x397fe69au, 0x1a0111eau};
+        return t[i];
+    }
+    static constexpr uint32_t INV = 0xfffcfffdu;          // -p^-1 mod 2^32
+    B2_HD static constexpr uint32_t ONE(int i) {
+        constexpr uint32_t t[12] = {0x0002fffdu, 0x76090000u, 0xc40c0002u, 0xebf4000bu, 0x53c758bau, 0x5f489857u,
+                                         0x70525745u, 0x77ce5853u, 0xa256ec6du, 0x5c071a97u, 0xfa80e493u, 0x15f65ec3u};
+        return t[i];
+    }  // 2^384 mod p
+    B2_HD static constexpr uint32_t R2(int i) {
+        constexpr uint32_t t[12] = {0x1c341746u, 0xf4df1f34u, 0x09d104f1u, 0x0a76e6a6u, 0x4c95b6d5u, 0x8de5476cu,
+                                        0x939d83c0u, 0x67eb88a9u, 0xb519952du, 0x9a793e85u, 0x92cae3aau, 0x11988fe5u};
+        return t[i];
+    }  // 2^768 mod p
+};
+
+// ----------------------------------------------------------------------- Fp<P>
+template <class PR> struct Fp {
+    static constexpr int N = PR::N;
+    uint32_t v[N];
+
+    B2_HD static Fp zero() { Fp r; for (int i = 0; i < N; ++i) r.v[i] = 0; return r; }
+    B2_HD static Fp one() { Fp r; for (int i = 0; i < N; ++i) r.v[i] = PR::ONE(i); return r; }
+    B2_HD static Fp r2() { Fp r; for (int i = 0; i < N; ++i) r.v[i] = PR::R2(i); return r; }
+    B2_HD bool is_zero() const { uint32_t t = 0; for (int i = 0; i < N; ++i) t |= v[i]; return t == 0; }
+    B2_HD bool operator==(const Fp& o) const { uint32_t t = 0; for (int i = 0; i < N; ++i) t |= v[i] ^ o.v[i]; return t == 0; }
+    B2_HD bool operator!=(const Fp& o) const { return !(*this == o); }
+
+    // t >= p ?  (raw limb compare; used for canonical-input validation)
+    B2_HD static bool geq_p(const uint32_t* t) {
+        for (int i = N - 1; i >= 0; --i) {
+            if (t[i] != PR::P(i)) return t[i] > PR::P(i);
+        }
+        return true;
+    }
+
+    // r = t - p if t >= p else t   (t < 2p, optional extra top bit `hi`)
+    B2_HD static void final_sub(uint32_t* r, const uint32_t* t, uint32_t hi) {
+        uint32_t d[N];
+        d[0] = ptx::sub_cc(t[0], PR::P(0));
+#pragma unroll
+        for (int i = 1; i < N; ++i) d[i] = ptx::subc_cc(t[i], PR::P(i));
+        uint32_t b = ptx::subc(hi, 0);          // 0 if t >= p (no borrow), 0xffffffff if borrow
+        bool keep = (b != 0);
+#pragma unroll
+        for (int i = 0; i < N; ++i) r[i] = keep ? t[i] : d[i];
+    }
+
+    B2_HD Fp operator+(const Fp& o) const {
+        uint32_t t[N];
+        t[0] = ptx::add_cc(v[0], o.v[0]);
+#pragma unroll
+        for (int i = 1; i < N; ++i) t[i] = ptx::addc_cc(v[i], o.v[i]);
+        uint32_t hi = ptx::addc(0, 0);          // p < 2^(32N-1) so hi is always 0, kept for safety
+        Fp r; final_sub(r.v, t, hi); return r;
+    }
+    B2_HD Fp operator-(const Fp& o) const {
+        Fp r;
+        r.v[0] = ptx::sub_cc(v[0], o.v[0]);
+#pragma unroll
+        for (int i = 1; i < N; ++i) r.v[i] = ptx::subc_cc(v[i], o.v[i]);
+        uint32_t mask = ptx::subc(0, 0);        // all ones if borrow
+        r.v[0] = ptx::add_cc(r.v[0], PR::P(0) & mask);
+#pragma unroll
+        for (int i = 1; i < N - 1; ++i) r.v[i] = ptx::addc_cc(r.v[i], PR::P(i) & mask);
+        r.v[N - 1] = ptx::addc(r.v[N - 1], PR::P(N - 1) & mask);
+        return r;
+    }
+    B2_HD Fp neg() const { return zero() - *this; }
+    B2_HD Fp dbl() const { return *this + *this; }
+
+    // acc[0..N) (+carry into *top) += a[start], a[start+2], ... times b on aligned pairs
+    //   (acc[0],acc[1]) += a[start]*b ; (acc[2],acc[3]) += a[start+2]*b ; ...
+    // `carry_in` says whether CC.CF already holds a carry for position 0.
+    template <bool CARRY_IN>
+    B2_HD static void mad_row(uint32_t* acc, const uint32_t* a, int start, uint32_t b) {
+        acc[0] = CARRY_IN ? ptx::madc_lo_cc(a[start], b, acc[0]) : ptx::mad_lo_cc(a[start], b, acc[0]);
+        acc[1] = ptx::madc_hi_cc(a[start], b, acc[1]);
+#pragma unroll
+        for (int j = 2; j < N; j += 2) {
+            acc[j] = ptx::madc_lo_cc(a[start + j], b, acc[j]);
+            acc[j + 1] = ptx::madc_hi_cc(a[start + j], b, acc[j + 1]);
+        }
+    }
+
+    // Montgomery product.  Invariant per outer step: the running value is
+    //   T = sum E[k] 2^(32k) + sum O[k] 2^(32(k+1)),  T < 2p.
+    B2_HD Fp operator*(const Fp& o) const {
+        uint32_t E[N], O[N], pl[N];
+#pragma unroll
+        for (int i = 0; i < N; ++i) { E[i] = 0; O[i] = 0; pl[i] = PR::P(i); }
+        uint32_t stray = 0;                     // limb of weight 2^0 left over by the previous shift
+#pragma unroll
+        for (int i = 0; i < N; ++i) {
+            const uint32_t bi = o.v[i];
+            // multiply step: T += a * b_i
+            E[0] = ptx::add_cc(E[0], stray);
+            mad_row<true>(O, v, 1, bi);         // carry of the stray add enters at weight 2^32
+            // (no carry can leave O: T + a*b_i < 2^(32(N+1)))
+            mad_row<false>(E, v, 0, bi);
+            O[N - 1] = ptx::addc(O[N - 1], 0);
+            // reduce step: T += m * p with m chosen so T = 0 mod 2^32
+            const uint32_t m = E[0] * PR::INV;
+            mad_row<false>(O, pl, 1, m);
+            mad_row<false>(E, pl, 0, m);
+            O[N - 1] = ptx::addc(O[N - 1], 0);
+            // shift right one limb: E' = O, O'[k] = E[k+2], stray' = E[1]
+            stray = E[1];
+            uint32_t nE[N];
+#pragma unroll
+            for (int k = 0; k < N; ++k) nE[k] = O[k];
+#pragma unroll
+            for (int k = 0; k < N - 2; ++k) O[k] = E[k + 2];
+            O[N - 2] = 0; O[N - 1] = 0;
+#pragma unroll
+            for (int k = 0; k < N; ++k) E[k] = nE[k];
+        }
+        // fold: T = E + stray + (O << 32)
+        uint32_t t[N];
+        t[0] = ptx::add_cc(E[0], stray);
+#pragma unroll
+        for (int k = 1; k < N; ++k) t[k] = ptx::addc_cc(E[k], O[k - 1]);
+        uint32_t hi = ptx::addc(O[N - 1], 0);
+        Fp r; final_sub(r.v, t, hi); return r;
+    }
+    B2_HD Fp sqr() const { return *this * *this; }
+
+    // canonical (non-Montgomery) limbs <-> Montgomery
+    B2_HD static Fp from_canonical(const uint32_t* c) { Fp t; for (int i = 0; i < N; ++i) t.v[i] = c[i]; return t * r2(); }
+    B2_HD void to_canonical(uint32_t* c) const {
+        Fp o = zero(); o.v[0] = 1;
+        Fp t = *this * o;
+        for (int i = 0; i < N; ++i) c[i] = t.v[i];
+    }
+
+    // a^e for a public exponent given as limbs (square-and-multiply, MSB first)
+    B2_HD Fp pow_limbs(const uint32_t* e, int n) const {
+        Fp r = one();
+        for (int i = n * 32 - 1; i >= 0; --i) {
+            r = r.sqr();
+            if ((e[i >> 5] >> (i & 31)) & 1) r = r * *this;
+        }
+        return r;
+    }
+    // Fermat inverse a^(p-2); inv(0) = 0
+    B2_HD Fp inv() const {
+        uint32_t e[N];
+        uint32_t borrow = 2;                    // e = p - 2 with borrow propagation (r[0] == 1)
+        for (int i = 0; i < N; ++i) {
+            uint32_t pi = PR::P(i);
+            e[i] = pi - borrow;
+            borrow = (pi < borrow) ? 1u : 0u;
+        }
+        return pow_limbs(e, N);
+    }
+};
+
+typedef Fp<FrParams> Fr;
+typedef Fp<FqParams> Fq;
+
+// ------------------------------------------------------------------------- Fq2
+// Fq[u]/(u^2+1).  mul = 3 Fq products (Karatsuba), sqr = 2.
+struct Fq2 {
+    Fq c0, c1;
+    B2_HD static Fq2 zero() { return {Fq::zero(), Fq::zero()}; }
+    B2_HD static Fq2 one() { return {Fq::one(), Fq::zero()}; }
+    B2_HD bool is_zero() const { return c0.is_zero() && c1.is_zero(); }
+    B2_HD bool operator==(const Fq2& o) const { return c0 == o.c0 && c1 == o.c1; }
+    B2_HD bool operator!=(const Fq2& o) const { return !(*this == o); }
+    B2_HD Fq2 operator+(const Fq2& o) const { return {c0 + o.c0, c1 + o.c1}; }
+    B2_HD Fq2 operator-(const Fq2& o) const { return {c0 - o.c0, c1 - o.c1}; }
+    B2_HD Fq2 neg() const { return {c0.neg(), c1.neg()}; }
+    B2_HD Fq2 dbl() const { return {c0.dbl(), c1.dbl()}; }
+    B2_HD Fq2 operator*(const Fq2& o) const {
+        Fq ac = c0 * o.c0, bd = c1 * o.c1;
+        Fq t = (c0 + c1) * (o.c0 + o.c1);
+        return {ac - bd, t - ac - bd};
+    }
+    B2_HD Fq2 sqr() const {
+        Fq ab = c0 * c1;
+        return {(c0 + c1) * (c0 - c1), ab.dbl()};
+    }
+    B2_HD Fq2 inv() const {
+        Fq n = (c0.sqr() + c1.sqr()).inv();
+        return {c0 * n, (c1 * n).neg()};
+    }
+};
+
+}  // namespace b2

@@ -1,0 +1,202 @@
+// Fr radix-2 NTT as a sequence of shared-memory passes (multi-step / "four-step"
+// decomposition).  Replaces crypto3-math `evaluation_domain<Fr>::fft / inverse_fft` and
+// the coset multiplies used by the r1cs_to_qap witness map (un-vendored).
+//
+// A transform of size N = 2^log_n is split into passes p = 0..P-1 with k_p index bits
+// each (sum k_p = log_n).  Pass p sees the vector as contiguous blocks of size 2^L_p
+// (L_0 = log_n, L_{p+1} = L_p - k_p); inside a block it runs 2^(L_p-k_p) independent
+// size-2^k_p NTTs along stride S_p = 2^(L_p-k_p) with *pure* 2^k_p-th roots, and
+// multiplies element (k1, i2) by the inter-pass twiddle w_N^((i2*k1) << (log_n-L_p)).
+//   NR order ("natural -> digit-reversed"): passes 0..P-1, twiddle AFTER the small NTT.
+//   RN order ("digit-reversed -> natural"): passes P-1..0, twiddle BEFORE the small NTT
+//   (the exact transpose of NR).  Memory position with pass digits (d_0,..,d_{P-1})
+//   (top to bottom) holds spectrum/coefficient index d_0 + 2^k_0 d_1 + 2^(k_0+k_1) d_2 ...
+// The witness map chains NR(inverse) -> RN(forward, coset) -> pointwise -> NR(inverse)
+// so no reordering pass is ever needed; only the public natural-order API permutes.
+//
+// One CTA owns a tile of 2^(k+logc) <= 2048 elements (64 KB of shared memory as two
+// uint4 planes -> conflict-free 128-bit accesses): 2^k rows x 2^logc columns.  Strided
+// passes take 2^logc *adjacent* columns so every global row access is 2^logc*32 B
+// contiguous; the last pass is fully contiguous.  HBM traffic: one read + one write of
+// the vector per pass (2*N*32 B), everything else stays on chip.
+//
+// The kernel body is written as barrier-free *phases* (load / stage / store) so that
+// tests/host_emu can execute the identical index arithmetic on the CPU.
+#pragma once
+#include "fp.cuh"
+
+namespace b2 {
+
+constexpr int NTT_TILE_LOG = 11;           // 2048 elements = 64 KB
+constexpr int NTT_ROOT_LOG = 11;           // in-tile root table: w_{2^11}^j, j < 1024
+constexpr int NTT_MAX_PASSES = 4;
+
+struct NttDigits {                         // pass split, top to bottom
+    int n_pass;
+    int k[NTT_MAX_PASSES];
+    int log_n;
+};
+
+// spectrum/coefficient index stored at memory position `pos` in digit-reversed layouts
+B2_HD uint64_t ntt_digit_index(const NttDigits& d, uint64_t pos) {
+    int L = d.log_n, shift = 0;
+    uint64_t idx = 0;
+    for (int p = 0; p < d.n_pass; ++p) {
+        L -= d.k[p];
+        idx |= ((pos >> L) & ((1ull << d.k[p]) - 1)) << shift;
+        shift += d.k[p];
+    }
+    return idx;
+}
+
+struct NttPass {
+    int log_n, L, k, logc;      // block log-size, row bits, column bits of the tile
+    int contiguous;             // 1: last pass (rows contiguous, columns = adjacent blocks)
+    int tw_mode;                // 0 none, 1 after small NTT (NR), 2 before (RN)
+    int scale_mode;             // 0 none, 1 on load, 2 on store
+    int scale_kind;             // 0: constant cscale; 1: g-power table at natural position;
+                                // 2: g-power table at digit-reversed index of the position
+    const Fr* roots;            // w_{2^11}^j  (forward or inverse set)
+    const Fr* tlo; const Fr* thi; int lo_bits;      // w_N^e = tlo[e & mask] * thi[e >> lo_bits]
+    const Fr* glo; const Fr* ghi; int g_lo_bits;    // scale(e) = glo[e & mask] * ghi[e >> g_lo_bits]
+    Fr cscale;
+    NttDigits digits;
+};
+
+struct Fr2x { uint4 lo, hi; };
+B2_HD Fr fr_from_planes(const uint4& lo, const uint4& hi) {
+    Fr r; r.v[0] = lo.x; r.v[1] = lo.y; r.v[2] = lo.z; r.v[3] = lo.w; r.v[4] = hi.x; r.v[5] = hi.y; r.v[6] = hi.z; r.v[7] = hi.w; return r;
+}
+B2_HD void fr_to_planes(const Fr& f, uint4& lo, uint4& hi) {
+    lo.x = f.v[0]; lo.y = f.v[1]; lo.z = f.v[2]; lo.w = f.v[3]; hi.x = f.v[4]; hi.y = f.v[5]; hi.z = f.v[6]; hi.w = f.v[7];
+}
+B2_HD Fr fr_load(const Fr* p) {
+    const uint4* q = reinterpret_cast<const uint4*>(p);
+    uint4 lo = q[0], hi = q[1];
+    return fr_from_planes(lo, hi);
+}
+B2_HD void fr_store(Fr* p, const Fr& f) {
+    uint4 lo, hi; fr_to_planes(f, lo, hi);
+    uint4* q = reinterpret_cast<uint4*>(p);
+    q[0] = lo; q[1] = hi;
+}
+
+B2_HD uint32_t bitrev_u32(uint32_t x, int bits) {
+    uint32_t r = 0;
+    for (int i = 0; i < bits; ++i) { r = (r << 1) | (x & 1); x >>= 1; }
+    return r;
+}
+
+// ---- tile geometry -------------------------------------------------------------
+// tile element e in [0, 2^(k+logc)):  (row, col) and its global position.
+struct NttTile {
+    int k, logc, contiguous;
+    uint64_t base;          // global position of (row 0, col 0)
+    uint64_t row_stride;    // global stride between rows
+    uint64_t col0;          // first column index inside the block (i2 of col 0), strided passes
+    B2_HD int row_of(int e) const { return contiguous ? (e & ((1 << k) - 1)) : (e >> logc); }
+    B2_HD int col_of(int e) const { return contiguous ? (e >> k) : (e & ((1 << logc) - 1)); }
+    B2_HD int elem(int row, int col) const { return contiguous ? ((col << k) | row) : ((row << logc) | col); }
+    B2_HD uint64_t gpos(int row, int col) const {
+        return contiguous ? base + ((uint64_t)col << k) + row : base + (uint64_t)row * row_stride + col;
+    }
+};
+
+B2_HD NttTile ntt_make_tile(const NttPass& p, uint64_t tile_id) {
+    NttTile t; t.k = p.k; t.logc = p.logc; t.contiguous = p.contiguous;
+    if (p.contiguous) {
+        t.base = tile_id << (p.k + p.logc); t.row_stride = 1; t.col0 = 0;
+    } else {
+        int s_log = p.L - p.k;                         // columns per block = 2^s_log
+        uint64_t tiles_per_block = 1ull << (s_log - p.logc);
+        uint64_t blk = tile_id / tiles_per_block, cg = tile_id % tiles_per_block;
+        t.col0 = cg << p.logc;
+        t.row_stride = 1ull << s_log;
+        t.base = (blk << p.L) + t.col0;
+    }
+    return t;
+}
+
+B2_HD Fr ntt_twiddle(const NttPass& p, uint64_t i2, uint32_t k1) {
+    uint64_t e = (i2 * k1) << (p.log_n - p.L);
+    uint32_t lo = (uint32_t)(e & ((1ull << p.lo_bits) - 1)), hi = (uint32_t)(e >> p.lo_bits);
+    Fr t = fr_load(p.tlo + lo);
+    if (hi) t = t * fr_load(p.thi + hi);
+    return t;
+}
+B2_HD Fr ntt_scale(const NttPass& p, uint64_t pos) {
+    if (p.scale_kind == 0) return p.cscale;
+    uint64_t e = (p.scale_kind == 1) ? pos : ntt_digit_index(p.digits, pos);
+    uint32_t lo = (uint32_t)(e & ((1ull << p.g_lo_bits) - 1)), hi = (uint32_t)(e >> p.g_lo_bits);
+    Fr t = fr_load(p.glo + lo);
+    if (hi) t = t * fr_load(p.ghi + hi);
+    return t;
+}
+
+// ---- phases (each is data-parallel over `e`; barriers only between phases) ------
+B2_HD void ntt_phase_load(const NttPass& p, const NttTile& t, const Fr* data, uint4* s_lo, uint4* s_hi, int e) {
+    int row = t.row_of(e), col = t.col_of(e);
+    uint64_t g = t.gpos(row, col);
+    Fr x = fr_load(data + g);
+    if (p.scale_mode == 1) x = x * ntt_scale(p, g);
+    if (p.tw_mode == 2 && row != 0) x = x * ntt_twiddle(p, t.col0 + col, (uint32_t)row);
+    fr_to_planes(x, s_lo[e], s_hi[e]);
+}
+// DIF butterfly `b` of the stage with half-size h = 2^hs
+B2_HD void ntt_phase_stage(const NttPass& p, const NttTile& t, uint4* s_lo, uint4* s_hi, int hs, int b) {
+    int half_rows = 1 << (p.k - 1);
+    int rb, col;
+    if (t.contiguous) { rb = b & (half_rows - 1); col = b >> (p.k - 1); }
+    else { col = b & ((1 << p.logc) - 1); rb = b >> p.logc; }
+    int h = 1 << hs;
+    int j = rb & (h - 1), grp = rb >> hs;
+    int r0 = (grp << (hs + 1)) | j;
+    int e0 = t.elem(r0, col), e1 = t.elem(r0 + h, col);
+    Fr u = fr_from_planes(s_lo[e0], s_hi[e0]);
+    Fr v = fr_from_planes(s_lo[e1], s_hi[e1]);
+    Fr s = u + v, d = u - v;
+    if (j) d = d * fr_load(p.roots + ((uint32_t)j << (NTT_ROOT_LOG - 1 - hs)));
+    fr_to_planes(s, s_lo[e0], s_hi[e0]);
+    fr_to_planes(d, s_lo[e1], s_hi[e1]);
+}
+B2_HD void ntt_phase_store(const NttPass& p, const NttTile& t, Fr* data, const uint4* s_lo, const uint4* s_hi, int e) {
+    int row = t.row_of(e), col = t.col_of(e);          // output row k1 (natural order)
+    int src = t.elem((int)bitrev_u32((uint32_t)row, p.k), col);
+    Fr x = fr_from_planes(s_lo[src], s_hi[src]);
+    uint64_t g = t.gpos(row, col);
+    if (p.tw_mode == 1 && row != 0) x = x * ntt_twiddle(p, t.col0 + col, (uint32_t)row);
+    if (p.scale_mode == 2) x = x * ntt_scale(p, g);
+    fr_store(data + g, x);
+}
+
+#if defined(__CUDACC__)
+__global__ void __launch_bounds__(256) ntt_pass_kernel(Fr* data, const NttPass p) {
+    extern __shared__ uint4 smem[];
+    const int T = 1 << (p.k + p.logc);
+    uint4* s_lo = smem;
+    uint4* s_hi = smem + T;
+    for (uint64_t tile_id = blockIdx.x; tile_id < ((1ull << p.log_n) >> (p.k + p.logc)); tile_id += gridDim.x) {
+        const NttTile t = ntt_make_tile(p, tile_id);
+        for (int e = threadIdx.x; e < T; e += blockDim.x) ntt_phase_load(p, t, data, s_lo, s_hi, e);
+        __syncthreads();
+        for (int hs = p.k - 1; hs >= 0; --hs) {
+            for (int b = threadIdx.x; b < T / 2; b += blockDim.x) ntt_phase_stage(p, t, s_lo, s_hi, hs, b);
+            __syncthreads();
+        }
+        for (int e = threadIdx.x; e < T; e += blockDim.x) ntt_phase_store(p, t, data, s_lo, s_hi, e);
+        __syncthreads();
+    }
+}
+
+// out[digit_index(pos)] = in[pos]  (digit-reversed -> natural), or the inverse gather
+__global__ void ntt_permute_kernel(const Fr* in, Fr* out, NttDigits d, int to_natural) {
+    uint64_t n = 1ull << d.log_n;
+    for (uint64_t pos = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; pos < n; pos += (uint64_t)gridDim.x * blockDim.x) {
+        uint64_t idx = ntt_digit_index(d, pos);
+        if (to_natural) fr_store(out + idx, fr_load(in + pos));
+        else fr_store(out + pos, fr_load(in + idx));
+    }
+}
+#endif
+
+}  // namespace b2

@@ -1,0 +1,172 @@
+/* libb2g16 -- B200-native Groth16 (r1cs_gg_ppzksnark, BLS12-381) proving backend.
+ *
+ * C ABI that stands where crypto3-fil-proofs calls into the (header-only, un-vendored)
+ * crypto3 suite for its SNARK hot path.  The reference has no FFI layer: its callers
+ * name C++ templates directly, so each entry point below cites the reference call site
+ * or type it replaces (paths relative to the reference root;
+ *   S/ = libs/storage/include/nil/filecoin/storage/proofs/
+ *   F/ = libs/filecoin/include/nil/filecoin/proofs/).
+ * INTEGRATION.md shows the C++ shim (`nil::crypto3::...` names) a maintainer binds.
+ *
+ * Data formats (Montgomery form never crosses the ABI):
+ *   Fr  : 32 bytes little-endian, canonical (< r)            S/core/fr32.hpp:36-52
+ *   G1  : affine x||y, 48-byte LE canonical each (96 B); identity = 96 zero bytes
+ *   G2  : affine x.c0||x.c1||y.c0||y.c1 (192 B); identity = 192 zero bytes
+ *   proof : 192 bytes = compressed A(48)||B(96)||C(48), big-endian with flag bits
+ *           (F/constants.hpp:93 SINGLE_PARTITION_PROOF_LEN; F/api/seal.hpp:306-308)
+ * Every function returns 0 on success or a negative B2G16_E_* code; the message is
+ * available from b2g16_last_error().  No exceptions cross the ABI.  There is no CPU
+ * fallback: without a CUDA device b2g16_init fails with B2G16_E_CUDA.
+ * Host pointers unless a parameter name starts with d_ (device pointer).
+ */
+#ifndef B2G16_H
+#define B2G16_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2G16_OK 0
+#define B2G16_E_INVALID_ARG (-1)
+#define B2G16_E_NOT_CANONICAL (-2)  /* Fr >= r or coordinate >= p (fr32 contract)            */
+#define B2G16_E_NOT_ON_CURVE (-3)
+#define B2G16_E_CUDA (-4)
+#define B2G16_E_NCCL (-5)
+#define B2G16_E_OOM (-6)
+#define B2G16_E_INTERNAL (-7)
+
+typedef struct b2g16_ctx b2g16_ctx;
+typedef struct b2g16_pk b2g16_pk;
+
+/* One context per process/GPU (one process per GPU; ranks are independent).
+ * `stream` is a cudaStream_t (e.g. torch.cuda.current_stream().cuda_stream) or NULL for a
+ * library-owned stream.  All work is ordered on that stream. */
+int b2g16_init(int device, void* stream, b2g16_ctx** out);
+int b2g16_shutdown(b2g16_ctx* ctx);
+const char* b2g16_last_error(b2g16_ctx* ctx);
+int b2g16_synchronize(b2g16_ctx* ctx);
+/* number of kernels this library has launched on ctx so far */
+uint64_t b2g16_launch_count(b2g16_ctx* ctx);
+
+/* ---- multiexp: replaces algebra::multiexp / multiexp_with_mixed_addition,
+ *      used for the a / b_g1 / b_g2 / l / h queries of S/core/crypto/scheme_params.hpp:46-66.
+ *      out = sum_i scalars[i] * bases[i] in affine ABI encoding. */
+int b2g16_msm_g1(b2g16_ctx*, const uint8_t* bases96, const uint8_t* scalars32, size_t n, uint8_t out96[96]);
+int b2g16_msm_g2(b2g16_ctx*, const uint8_t* bases192, const uint8_t* scalars32, size_t n, uint8_t out192[192]);
+
+/* Device-resident bases (the proving-key residency of F/caches.hpp:48-67
+ * GROTH_PARAM_MEMORY_CACHE): upload once, multiply many times. */
+typedef struct b2g16_bases b2g16_bases;
+int b2g16_bases_upload_g1(b2g16_ctx*, const uint8_t* bases96, size_t n, b2g16_bases** out);
+int b2g16_bases_upload_g2(b2g16_ctx*, const uint8_t* bases192, size_t n, b2g16_bases** out);
+/* bases[i] = k_i * G for the canonical scalars d_k (synthetic inputs for benchmarks) */
+int b2g16_bases_generate(b2g16_ctx*, int group /*1|2*/, const uint8_t* d_scalars32, size_t n, b2g16_bases** out);
+int b2g16_bases_download(b2g16_ctx*, const b2g16_bases*, size_t first, size_t count, uint8_t* out);
+size_t b2g16_bases_count(const b2g16_bases*);
+int b2g16_bases_free(b2g16_ctx*, b2g16_bases*);
+/* scalars already in device memory (32-byte canonical each); result to host.
+ * Uses points [first, first+n) of the resident set (MSM range-sharding across ranks). */
+int b2g16_msm_resident(b2g16_ctx*, const b2g16_bases*, size_t first, const uint8_t* d_scalars32, size_t n, uint8_t* out_affine);
+/* same, asynchronous: writes the affine result (96/192 B) to device memory d_out */
+int b2g16_msm_resident_async(b2g16_ctx*, const b2g16_bases*, size_t first, const uint8_t* d_scalars32, size_t n, uint8_t* d_out_affine);
+/* out = sum of n affine points (combining per-GPU partial MSM results after all-gather) */
+int b2g16_g1_sum(b2g16_ctx*, const uint8_t* pts96, size_t n, uint8_t out96[96]);
+int b2g16_g2_sum(b2g16_ctx*, const uint8_t* pts192, size_t n, uint8_t out192[192]);
+
+/* ---- evaluation_domain: replaces math::evaluation_domain<Fr>::fft / inverse_fft and the
+ *      coset variants.  Natural order in and out, size 2^log_n, in place.
+ *      coset uses the multiplicative generator g = 7: forward evaluates on g*D,
+ *      inverse interpolates from g*D. */
+int b2g16_ntt(b2g16_ctx*, uint8_t* fr32_inout, unsigned log_n, int inverse, int coset);
+/* device-resident variant: d_data holds 2^log_n canonical 32-byte scalars */
+int b2g16_ntt_device(b2g16_ctx*, uint8_t* d_fr32_inout, unsigned log_n, int inverse, int coset);
+
+/* ---- r1cs_to_qap witness map tail: a,b,c evaluations on the domain ->
+ *      coefficients of H = (A*B - C)/Z  (m values, h[m-1] = 0). */
+int b2g16_h_from_abc(b2g16_ctx*, const uint8_t* a32, const uint8_t* b32, const uint8_t* c32, unsigned log_m, uint8_t* h32_out);
+
+/* ---- constraint system + proving key -------------------------------------------------- */
+typedef struct {
+    uint64_t n_rows, nnz;
+    const uint32_t* row_ptr; /* n_rows + 1 */
+    const uint32_t* col;     /* nnz  */
+    const uint8_t* val;      /* nnz * 32, canonical Fr */
+} b2g16_csr;
+
+typedef struct {
+    uint32_t log_m;          /* domain size 2^log_m >= n_cons + n_in + 1 (radix-2 only) */
+    uint64_t n_cons, n_in, n_aux; /* variables z = (1, x_1..x_nin, w_1..w_naux) */
+    b2g16_csr A, B, C;
+} b2g16_r1cs_view;
+
+/* Mirrors scheme_params<r1cs_gg_ppzksnark<bls12<381>>> (S/core/crypto/scheme_params.hpp:38-67)
+ * in the dense crypto3 layout: one base per variable, identity where the polynomial is zero. */
+typedef struct {
+    const uint8_t *alpha_g1, *beta_g1, *delta_g1; /* 96 B   */
+    const uint8_t *beta_g2, *delta_g2;            /* 192 B  */
+    const uint8_t* a;    /* n_vars * 96  */
+    const uint8_t* b_g1; /* n_vars * 96  */
+    const uint8_t* b_g2; /* n_vars * 192 */
+    const uint8_t* l;    /* n_aux  * 96  */
+    const uint8_t* h;    /* (m-1)  * 96  */
+    const b2g16_r1cs_view* cs;
+} b2g16_pk_view;
+
+/* Copies key + constraint system to the device (caller keeps its buffers). */
+int b2g16_pk_load(b2g16_ctx*, const b2g16_pk_view*, b2g16_pk** out);
+int b2g16_pk_free(b2g16_ctx*, b2g16_pk*);
+
+/* Groth16 setup from explicit toxic waste (tau, alpha, beta, gamma, delta; 5*32 B), computed
+ * on the device (fixed-base multiplications).  Benchmark/test support for synthetic keys
+ * (S/core/parameter_cache.hpp:185-200 generates throw-away params the same way).
+ * vk_out (optional): alpha_g1(96) beta_g2(192) gamma_g2(192) delta_g2(192) then (n_in+1) IC (96 each). */
+int b2g16_pk_generate(b2g16_ctx*, const b2g16_r1cs_view* cs, const uint8_t toxic[160], b2g16_pk** out, uint8_t* vk_out);
+/* read back one query for parity tests: which = 0 a, 1 b_g1, 2 b_g2, 3 l, 4 h,
+ * 5 alpha_g1, 6 beta_g1, 7 delta_g1, 8 beta_g2, 9 delta_g2 */
+int b2g16_pk_export(b2g16_ctx*, const b2g16_pk*, int which, uint8_t* out, size_t out_bytes);
+
+/* Optional trace of every intermediate (any pointer may be NULL). Host buffers. */
+typedef struct {
+    uint8_t *a, *b, *c;                      /* m*32 evaluations             */
+    uint8_t* h;                              /* m*32 coefficients            */
+    uint8_t *msm_a, *msm_b1, *msm_l, *msm_h; /* 96  */
+    uint8_t* msm_b2;                         /* 192 */
+    uint8_t *A, *C;                          /* 96 affine proof points */
+    uint8_t* B;                              /* 192 */
+    float stage_ms[8]; /* out: ingest, abc(spmv), ntt/h, msm_a, msm_b1, msm_b2, msm_l, msm_h+final */
+} b2g16_trace;
+
+/* The prover: replaces r1cs_gg_ppzksnark prove(pk, primary, aux) as called from
+ * compound_proof::circuit_proofs (S/core/proof/compound_proof.hpp:127-137) on behalf of
+ * seal_commit_phase2 (F/api/seal.hpp:298-301) and generate_{window,winning}_post
+ * (F/api/post.hpp:225,345).  assignment32 = (1, inputs, aux) = 1+n_in+n_aux scalars.
+ * r, s are explicit (bit-exact parity); priority mirrors compound_proof.hpp:134. */
+int b2g16_prove(b2g16_ctx*, const b2g16_pk*, const uint8_t* assignment32, const uint8_t r32[32],
+                const uint8_t s32[32], int priority, uint8_t proof_out[192], b2g16_trace* trace);
+/* assignment already on the device; proof written to host */
+int b2g16_prove_device(b2g16_ctx*, const b2g16_pk*, const uint8_t* d_assignment32, const uint8_t r32[32],
+                       const uint8_t s32[32], int priority, uint8_t proof_out[192], b2g16_trace* trace);
+/* n_partitions independent witnesses for one key -> 192*n bytes (multi_proof, F/api/seal.hpp:304-308) */
+int b2g16_prove_batch(b2g16_ctx*, const b2g16_pk*, const uint8_t* assignments32, size_t n_partitions,
+                      const uint8_t* r32s, const uint8_t* s32s, int priority, uint8_t* proofs_out);
+
+/* ---- synthetic-instance support (bench/test): evaluate one layer of a forward-built R1CS on
+ *      the device: for rows [row0,row1): z[out_base + i] = (A_i . z) * (B_i . z).  d_z canonical. */
+int b2g16_synth_witness(b2g16_ctx*, const b2g16_pk*, uint8_t* d_assignment32, uint64_t n_free);
+
+/* ---- measurement: sustained 32x32+64 multiply-add rate of this GPU in MAD32/s
+ *      (the MSM roofline denominator) */
+int b2g16_measure_mad32_peak(b2g16_ctx*, double* mad32_per_s, double* elapsed_ms);
+/* last MSM's per-stage device times in ms: digits+histogram, scan, scatter, accumulate, reduce */
+int b2g16_last_msm_timing(b2g16_ctx*, float out_ms[5]);
+
+/* ---- elementwise field kernels exposed for parity tests (device does the arithmetic).
+ *      field: 0 = Fr (32 B), 1 = Fq (48 B); op: 0 add 1 sub 2 mul 3 inv 4 sqr 5 neg */
+int b2g16_field_op(b2g16_ctx*, int field, int op, const uint8_t* a, const uint8_t* b, size_t n, uint8_t* out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
