@@ -43,6 +43,8 @@ B2_D uint32_t mad_lo_cc(uint32_t a, uint32_t b, uint32_t c) { uint32_t r; asm vo
 B2_D uint32_t madc_lo_cc(uint32_t a, uint32_t b, uint32_t c) { uint32_t r; asm volatile("madc.lo.cc.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
 B2_D uint32_t madc_hi_cc(uint32_t a, uint32_t b, uint32_t c) { uint32_t r; asm volatile("madc.hi.cc.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
 B2_D uint32_t madc_hi(uint32_t a, uint32_t b, uint32_t c) { uint32_t r; asm volatile("madc.hi.u32 %0, %1, %2, %3;" : "=r"(r) : "r"(a), "r"(b), "r"(c)); return r; }
+B2_D uint32_t mul_lo(uint32_t a, uint32_t b) { uint32_t r; asm volatile("mul.lo.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
+B2_D uint32_t mul_hi(uint32_t a, uint32_t b) { uint32_t r; asm volatile("mul.hi.u32 %0, %1, %2;" : "=r"(r) : "r"(a), "r"(b)); return r; }
 #else
 // Host emulation: one carry flag per thread, same semantics as PTX CC.CF.
 inline uint32_t& cf() { static thread_local uint32_t f = 0; return f; }
@@ -56,6 +58,8 @@ inline uint32_t mad_lo_cc(uint32_t a, uint32_t b, uint32_t c) { uint64_t t = (ui
 inline uint32_t madc_lo_cc(uint32_t a, uint32_t b, uint32_t c) { uint64_t t = (uint64_t)(uint32_t)((uint64_t)a * b) + c + cf(); cf() = (uint32_t)(t >> 32); return (uint32_t)t; }
 inline uint32_t madc_hi_cc(uint32_t a, uint32_t b, uint32_t c) { uint64_t t = (((uint64_t)a * b) >> 32) + c + cf(); cf() = (uint32_t)(t >> 32); return (uint32_t)t; }
 inline uint32_t madc_hi(uint32_t a, uint32_t b, uint32_t c) { return (uint32_t)((((uint64_t)a * b) >> 32) + c + cf()); }
+inline uint32_t mul_lo(uint32_t a, uint32_t b) { return (uint32_t)((uint64_t)a * b); }
+inline uint32_t mul_hi(uint32_t a, uint32_t b) { return (uint32_t)(((uint64_t)a * b) >> 32); }
 #endif
 }  // namespace ptx
 
@@ -71,6 +75,8 @@ struct FrParams {
         return t[i];
     }
     static constexpr uint32_t INV = 0xffffffffu;          // -r^-1 mod 2^32
+    B2_HD static uint32_t mod_limb(int i);                // modulus / INV as the multiplier reads them
+    B2_HD static uint32_t inv_limb();                     // (constant memory on the device)
     B2_HD static constexpr uint32_t ONE(int i) {
         constexpr uint32_t t[8] = {0xfffffffeu, 0x00000001u, 0x00034802u, 0x5884b7fau,
                                         0xecbc4ff5u, 0x998c4fefu, 0xacc5056fu, 0x1824b159u};
@@ -91,6 +97,8 @@ struct FqParams {
         return t[i];
     }
     static constexpr uint32_t INV = 0xfffcfffdu;          // -p^-1 mod 2^32
+    B2_HD static uint32_t mod_limb(int i);
+    B2_HD static uint32_t inv_limb();
     B2_HD static constexpr uint32_t ONE(int i) {
         constexpr uint32_t t[12] = {0x0002fffdu, 0x76090000u, 0xc40c0002u, 0xebf4000bu, 0x53c758bau, 0x5f489857u,
                                          0x70525745u, 0x77ce5853u, 0xa256ec6du, 0x5c071a97u, 0xfa80e493u, 0x15f65ec3u};
@@ -102,6 +110,44 @@ struct FqParams {
         return t[i];
     }  // 2^768 mod p
 };
+
+#if defined(__CUDACC__)
+// Runtime-visible copies: ptxas must not constant-fold the modulus into the multiplier.
+static __device__ __constant__ uint32_t k_fr_mod[8] = {0x00000001u, 0xffffffffu, 0xfffe5bfeu, 0x53bda402u,
+                                                       0x09a1d805u, 0x3339d808u, 0x299d7d48u, 0x73eda753u};
+static __device__ __constant__ uint32_t k_fq_mod[12] = {0xffffaaabu, 0xb9feffffu, 0xb153ffffu, 0x1eabfffeu, 0xf6b0f624u, 0x6730d2a0u,
+                                                        0xf38512bfu, 0x64774b84u, 0x434bacd7u, 0x4b1ba7b6u, 0x397fe69au, 0x1a0111eau};
+static __device__ __constant__ uint32_t k_fr_inv = 0xffffffffu;
+static __device__ __constant__ uint32_t k_fq_inv = 0xfffcfffdu;
+#endif
+B2_HD uint32_t FrParams::mod_limb(int i) {
+#if defined(__CUDA_ARCH__)
+    return k_fr_mod[i];
+#else
+    return P(i);
+#endif
+}
+B2_HD uint32_t FrParams::inv_limb() {
+#if defined(__CUDA_ARCH__)
+    return k_fr_inv;
+#else
+    return INV;
+#endif
+}
+B2_HD uint32_t FqParams::mod_limb(int i) {
+#if defined(__CUDA_ARCH__)
+    return k_fq_mod[i];
+#else
+    return P(i);
+#endif
+}
+B2_HD uint32_t FqParams::inv_limb() {
+#if defined(__CUDA_ARCH__)
+    return k_fq_inv;
+#else
+    return INV;
+#endif
+}
 
 // ----------------------------------------------------------------------- Fp<P>
 template <class PR> struct Fp {
@@ -158,59 +204,71 @@ template <class PR> struct Fp {
     B2_HD Fp neg() const { return zero() - *this; }
     B2_HD Fp dbl() const { return *this + *this; }
 
-    // acc[0..N) (+carry into *top) += a[start], a[start+2], ... times b on aligned pairs
-    //   (acc[0],acc[1]) += a[start]*b ; (acc[2],acc[3]) += a[start+2]*b ; ...
-    // `carry_in` says whether CC.CF already holds a carry for position 0.
-    template <bool CARRY_IN>
-    B2_HD static void mad_row(uint32_t* acc, const uint32_t* a, int start, uint32_t b) {
-        acc[0] = CARRY_IN ? ptx::madc_lo_cc(a[start], b, acc[0]) : ptx::mad_lo_cc(a[start], b, acc[0]);
-        acc[1] = ptx::madc_hi_cc(a[start], b, acc[1]);
+    // acc pairs (acc[j], acc[j+1]) += a[j] * b for j = 0, 2, .., N-2, one carry chain.
+    // Each lo/hi pair is one IMAD.WIDE.U32(.X) in SASS.
+    B2_HD static void mad_pairs(uint32_t* acc, const uint32_t* a, uint32_t b) {
+        acc[0] = ptx::mad_lo_cc(a[0], b, acc[0]);
+        acc[1] = ptx::madc_hi_cc(a[0], b, acc[1]);
 #pragma unroll
         for (int j = 2; j < N; j += 2) {
-            acc[j] = ptx::madc_lo_cc(a[start + j], b, acc[j]);
-            acc[j + 1] = ptx::madc_hi_cc(a[start + j], b, acc[j + 1]);
+            acc[j] = ptx::madc_lo_cc(a[j], b, acc[j]);
+            acc[j + 1] = ptx::madc_hi_cc(a[j], b, acc[j + 1]);
         }
     }
-
-    // Montgomery product.  Invariant per outer step: the running value is
-    //   T = sum E[k] 2^(32k) + sum O[k] 2^(32(k+1)),  T < 2p.
-    B2_HD Fp operator*(const Fp& o) const {
-        uint32_t E[N], O[N], pl[N];
+    // One CIOS step on the split accumulator.  In the frame of this step `ev` holds the
+    // 64-bit columns at limb positions (0,1),(2,3),.. and `od` the columns (1,2),(3,4),..;
+    // on entry (unless FIRST) `od` is still the previous step's `ev`, i.e. not yet shifted
+    // down by the limb that the previous reduction zeroed.  T += a*bi; T += m*p; T >>= 32
+    // (the shift is the role swap done by the caller).
+    template <bool FIRST>
+    B2_HD static void mad_redc(uint32_t* ev, uint32_t* od, const uint32_t* a, uint32_t bi, const uint32_t* mod, uint32_t inv) {
+        if (FIRST) {
 #pragma unroll
-        for (int i = 0; i < N; ++i) { E[i] = 0; O[i] = 0; pl[i] = PR::P(i); }
-        uint32_t stray = 0;                     // limb of weight 2^0 left over by the previous shift
+            for (int j = 0; j < N; j += 2) { od[j] = ptx::mul_lo(a[j + 1], bi); od[j + 1] = ptx::mul_hi(a[j + 1], bi); }
 #pragma unroll
-        for (int i = 0; i < N; ++i) {
-            const uint32_t bi = o.v[i];
-            // multiply step: T += a * b_i
-            E[0] = ptx::add_cc(E[0], stray);
-            mad_row<true>(O, v, 1, bi);         // carry of the stray add enters at weight 2^32
-            // (no carry can leave O: T + a*b_i < 2^(32(N+1)))
-            mad_row<false>(E, v, 0, bi);
-            O[N - 1] = ptx::addc(O[N - 1], 0);
-            // reduce step: T += m * p with m chosen so T = 0 mod 2^32
-            const uint32_t m = E[0] * PR::INV;
-            mad_row<false>(O, pl, 1, m);
-            mad_row<false>(E, pl, 0, m);
-            O[N - 1] = ptx::addc(O[N - 1], 0);
-            // shift right one limb: E' = O, O'[k] = E[k+2], stray' = E[1]
-            stray = E[1];
-            uint32_t nE[N];
+            for (int j = 0; j < N; j += 2) { ev[j] = ptx::mul_lo(a[j], bi); ev[j + 1] = ptx::mul_hi(a[j], bi); }
+        } else {
+            ev[0] = ptx::add_cc(ev[0], od[1]);              // limb left over by the shift
 #pragma unroll
-            for (int k = 0; k < N; ++k) nE[k] = O[k];
-#pragma unroll
-            for (int k = 0; k < N - 2; ++k) O[k] = E[k + 2];
-            O[N - 2] = 0; O[N - 1] = 0;
-#pragma unroll
-            for (int k = 0; k < N; ++k) E[k] = nE[k];
+            for (int j = 0; j < N - 2; j += 2) {            // shifted columns + odd limbs of a
+                od[j] = ptx::madc_lo_cc(a[j + 1], bi, od[j + 2]);
+                od[j + 1] = ptx::madc_hi_cc(a[j + 1], bi, od[j + 3]);
+            }
+            od[N - 2] = ptx::madc_lo_cc(a[N - 1], bi, 0);
+            od[N - 1] = ptx::madc_hi(a[N - 1], bi, 0);
+            mad_pairs(ev, a, bi);
+            od[N - 1] = ptx::addc(od[N - 1], 0);
         }
-        // fold: T = E + stray + (O << 32)
-        uint32_t t[N];
-        t[0] = ptx::add_cc(E[0], stray);
+        // m is computed through an opaque mul.lo with `inv` read from constant memory:
+        // when ptxas can see m = -T[0] (Fr: inv = 2^32-1) it rewrites the reduction rows and
+        // stops pairing lo/hi into IMAD.WIDE (measured: 185 vs 137 FMA-pipe ops per Fr product).
+        const uint32_t m = ptx::mul_lo(ev[0], inv);
+        mad_pairs(od, mod + 1, m);
+        mad_pairs(ev, mod, m);
+        od[N - 1] = ptx::addc(od[N - 1], 0);
+    }
+
+    // Montgomery product (CIOS, 32-bit limbs, even/odd 64-bit columns; the classic
+    // carry-chain layout of GPU big-number code): N^2 + N^2 wide MADs + N low MULs.
+    B2_HD Fp operator*(const Fp& o) const {
+        static_assert(N % 2 == 0, "even limb count");
+        uint32_t ev[N], od[N], mod[N], a[N], b[N];
 #pragma unroll
-        for (int k = 1; k < N; ++k) t[k] = ptx::addc_cc(E[k], O[k - 1]);
-        uint32_t hi = ptx::addc(O[N - 1], 0);
-        Fp r; final_sub(r.v, t, hi); return r;
+        for (int i = 0; i < N; ++i) { mod[i] = PR::mod_limb(i); a[i] = v[i]; b[i] = o.v[i]; }   // operands in registers: the
+        // asm statements below are volatile, a memory-resident operand would be re-read per limb
+        const uint32_t inv = PR::inv_limb();
+#pragma unroll
+        for (int i = 0; i < N; i += 2) {
+            if (i == 0) mad_redc<true>(ev, od, a, b[0], mod, inv); else mad_redc<false>(ev, od, a, b[i], mod, inv);
+            mad_redc<false>(od, ev, a, b[i + 1], mod, inv);
+        }
+        // T = ev (columns at 0,2,..) + od shifted by the dropped limb; T < 2p < 2^(32N)
+        uint32_t t[N];
+        t[0] = ptx::add_cc(ev[0], od[1]);
+#pragma unroll
+        for (int k = 1; k < N - 1; ++k) t[k] = ptx::addc_cc(ev[k], od[k + 1]);
+        t[N - 1] = ptx::addc(ev[N - 1], 0);
+        Fp r; final_sub(r.v, t, 0); return r;
     }
     B2_HD Fp sqr() const { return *this * *this; }
 
