@@ -10,7 +10,6 @@
 
 #include "../../include/b2g16.h"
 #include "ec.cuh"
-#include "ntt_kernels.cuh"
 
 namespace b2 {
 
@@ -28,6 +27,10 @@ struct Ctx {
     Fr* roots_inv = nullptr;
     std::map<int, NttDomain*> domains;
     uint64_t launches = 0;              // kernels launched by this library (bench "gpu_launches")
+    float msm_ms[5] = {0, 0, 0, 0, 0};  // last timed MSM: digits+hist, scan, scatter, accumulate, reduce
+    bool time_msm = false;
+    int msm_window_override = 0;        // 0 = pick by size
+    void* fixed_base[2] = {nullptr, nullptr};   // generator tables (G1, G2), built on first use
 };
 
 struct CudaError { cudaError_t e; const char* what; const char* file; int line; };
@@ -66,25 +69,37 @@ inline int grid_for(size_t n, int block, int max_blocks = 148 * 16) {
 }
 
 // ---- entry points implemented across the .cu files (all operate on ctx->stream) ----
-// ingest.cu
-void fr_from_bytes_dev(Ctx* c, const uint8_t* d_bytes, Fr* d_out, size_t n, int* d_bad);     // canonical -> Montgomery
-void fr_to_bytes_dev(Ctx* c, const Fr* d_in, uint8_t* d_bytes, size_t n);                      // Montgomery -> canonical
-void g1_from_bytes_dev(Ctx* c, const uint8_t* d_bytes, G1Affine* d_out, size_t n, int* d_bad);
-void g2_from_bytes_dev(Ctx* c, const uint8_t* d_bytes, G2Affine* d_out, size_t n, int* d_bad);
-void g1_to_bytes_dev(Ctx* c, const G1Affine* d_in, uint8_t* d_bytes, size_t n);
-void g2_to_bytes_dev(Ctx* c, const G2Affine* d_in, uint8_t* d_bytes, size_t n);
+// ingest.cu : ABI byte formats <-> Montgomery limbs.  d_bad (optional) is OR-ed with 1 when a
+// value is not canonical (>= modulus), with 2 when a point is not on the curve.
+void fr_from_bytes_dev(Ctx* c, const uint8_t* d_bytes, Fr* d_out, size_t n, int* d_bad);
+void fr_to_bytes_dev(Ctx* c, const Fr* d_in, uint8_t* d_bytes, size_t n);
+void g1_from_bytes_dev(Ctx* c, const uint8_t* d_bytes, G1Affine* d_out, size_t n, int* d_bad, bool check_curve);
+void g2_from_bytes_dev(Ctx* c, const uint8_t* d_bytes, G2Affine* d_out, size_t n, int* d_bad, bool check_curve);
+void g1_to_bytes_dev(Ctx* c, const G1Affine* d_in, uint8_t* d_bytes, size_t n, cudaStream_t st);
+void g2_to_bytes_dev(Ctx* c, const G2Affine* d_in, uint8_t* d_bytes, size_t n, cudaStream_t st);
 void scalars_check_dev(Ctx* c, const uint8_t* d_bytes, size_t n, int* d_bad);
+void field_op_dev(Ctx* c, int field, int op, const uint8_t* d_a, const uint8_t* d_b, size_t n, uint8_t* d_out, int* d_bad);
+double mad32_peak_dev(Ctx* c, double* elapsed_ms);
 // ntt.cu
 NttDomain* ntt_domain(Ctx* c, int log_n);
 void ntt_free_domains(Ctx* c);
 void ntt_init_roots(Ctx* c);
-// natural-order in/out transform on Montgomery data (the evaluation_domain API)
+// natural-order in/out transform (the evaluation_domain API); src may equal dst, tmp needs
+// 2^log_n elements when log_n > 11; in_canon/out_canon fuse the canonical<->Montgomery steps.
+void ntt_natural_ex(Ctx* c, const Fr* src, Fr* dst, Fr* tmp, int log_n, bool inverse, bool coset,
+                    bool in_canon, bool out_canon, int* d_bad);
 void ntt_natural(Ctx* c, Fr* d_data, int log_n, bool inverse, bool coset);
-// witness-map chain: a,b,c evaluations (natural, Montgomery; destroyed) -> H coefficients
-// written to d_h_canonical as canonical 32-byte scalars in natural order.
-void h_from_abc_dev(Ctx* c, Fr* d_a, Fr* d_b, Fr* d_c, int log_m, uint32_t* d_h_canonical);
-// msm.cu : result in XYZZ (Montgomery) written to d_out
-void msm_g1_dev(Ctx* c, const G1Affine* d_bases, const uint32_t* d_scalars_canonical, size_t n, G1Xyzz* d_out, cudaStream_t st);
-void msm_g2_dev(Ctx* c, const G2Affine* d_bases, const uint32_t* d_scalars_canonical, size_t n, G2Xyzz* d_out, cudaStream_t st);
+bool ntt_needs_tmp(int log_n);
+// witness-map chain: a,b,c evaluations (natural order; destroyed) -> H coefficients written
+// to d_h_canonical as canonical 32-byte scalars in natural order.
+void h_from_abc_dev(Ctx* c, Fr* d_a, Fr* d_b, Fr* d_c, int log_m, uint32_t* d_h_canonical, bool in_canon, int* d_bad);
+// msm_g1.cu / msm_g2.cu : sum_i s_i P_i over resident Montgomery-affine bases and canonical
+// device scalars; the affine result is written to d_out_bytes in the ABI encoding (96 / 192 B).
+void msm_g1_dev(Ctx* c, const G1Affine* d_bases, const uint32_t* d_scalars, size_t n, uint8_t* d_out_bytes, cudaStream_t st, int window_bits);
+void msm_g2_dev(Ctx* c, const G2Affine* d_bases, const uint32_t* d_scalars, size_t n, uint8_t* d_out_bytes, cudaStream_t st, int window_bits);
+void gen_mul_g1_dev(Ctx* c, const uint32_t* d_scalars, size_t n, G1Affine* d_out);
+void gen_mul_g2_dev(Ctx* c, const uint32_t* d_scalars, size_t n, G2Affine* d_out);
+void sum_g1_dev(Ctx* c, const G1Affine* d_pts, size_t n, uint8_t* d_out_bytes);
+void sum_g2_dev(Ctx* c, const G2Affine* d_pts, size_t n, uint8_t* d_out_bytes);
 
 }  // namespace b2

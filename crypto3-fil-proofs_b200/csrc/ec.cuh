@@ -86,6 +86,15 @@ template <class F> struct Xyzz {
     }
 };
 
+#if defined(__CUDACC__)
+// Out-of-line group operations for everything except the bucket-accumulation loop
+// (code size / compile time; these run O(buckets) times, not O(points)).
+template <class F> static __device__ __noinline__ void xyzz_add_call(Xyzz<F>* a, const Xyzz<F>* b) { a->add(*b); }
+template <class F> static __device__ __noinline__ void xyzz_add_mixed_call(Xyzz<F>* a, const Affine<F>* b) { a->add_mixed(*b); }
+template <class F> static __device__ __noinline__ void xyzz_dbl_call(Xyzz<F>* a) { *a = a->dbl(); }
+template <class F> static __device__ __noinline__ void xyzz_to_affine_call(Affine<F>* r, const Xyzz<F>* a) { *r = a->to_affine(); }
+#endif
+
 typedef Affine<Fq> G1Affine;
 typedef Affine<Fq2> G2Affine;
 typedef Xyzz<Fq> G1Xyzz;

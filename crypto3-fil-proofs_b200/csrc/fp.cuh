@@ -150,7 +150,7 @@ B2_HD uint32_t FqParams::inv_limb() {
 }
 
 // ----------------------------------------------------------------------- Fp<P>
-template <class PR> struct Fp {
+template <class PR> struct alignas(16) Fp {
     static constexpr int N = PR::N;
     uint32_t v[N];
 
@@ -318,19 +318,33 @@ struct Fq2 {
     B2_HD Fq2 operator-(const Fq2& o) const { return {c0 - o.c0, c1 - o.c1}; }
     B2_HD Fq2 neg() const { return {c0.neg(), c1.neg()}; }
     B2_HD Fq2 dbl() const { return {c0.dbl(), c1.dbl()}; }
-    B2_HD Fq2 operator*(const Fq2& o) const {
+    B2_HD Fq2 mul_inline(const Fq2& o) const {
         Fq ac = c0 * o.c0, bd = c1 * o.c1;
         Fq t = (c0 + c1) * (o.c0 + o.c1);
         return {ac - bd, t - ac - bd};
     }
-    B2_HD Fq2 sqr() const {
+    B2_HD Fq2 sqr_inline() const {
         Fq ab = c0 * c1;
         return {(c0 + c1) * (c0 - c1), ab.dbl()};
     }
+    // On the device the Fq2 product is an out-of-line call: three inlined 12-limb products
+    // per call site made G2 kernels too large to compile (and to fit the instruction cache).
+    B2_HD Fq2 operator*(const Fq2& o) const;
+    B2_HD Fq2 sqr() const;
     B2_HD Fq2 inv() const {
         Fq n = (c0.sqr() + c1.sqr()).inv();
         return {c0 * n, (c1 * n).neg()};
     }
 };
+
+#if defined(__CUDA_ARCH__)
+static __device__ __noinline__ void fq2_mul_call(Fq2* r, const Fq2* a, const Fq2* b) { *r = a->mul_inline(*b); }
+static __device__ __noinline__ void fq2_sqr_call(Fq2* r, const Fq2* a) { *r = a->sqr_inline(); }
+B2_HD Fq2 Fq2::operator*(const Fq2& o) const { Fq2 r; fq2_mul_call(&r, this, &o); return r; }
+B2_HD Fq2 Fq2::sqr() const { Fq2 r; fq2_sqr_call(&r, this); return r; }
+#else
+B2_HD Fq2 Fq2::operator*(const Fq2& o) const { return mul_inline(o); }
+B2_HD Fq2 Fq2::sqr() const { return sqr_inline(); }
+#endif
 
 }  // namespace b2

@@ -1,0 +1,340 @@
+// Pippenger multi-scalar multiplication for G1 (F = Fq) and G2 (F = Fq2) on sm_100a.
+// Replaces crypto3-algebra `multiexp<BDLO12>` / `multiexp_with_mixed_addition`
+// (un-vendored) for the a / b_g1 / b_g2 / l / h queries of
+// libs/storage/include/nil/filecoin/storage/proofs/core/crypto/scheme_params.hpp:46-66.
+//
+// Pipeline (all windows at once, one launch per step):
+//   1. signed-digit decomposition (window c bits, W = ceil(256/c) windows, digit in
+//      [-2^(c-1), 2^(c-1)], zero digits dropped) + histogram of (window, |digit|) buckets
+//   2. exclusive scan of the histogram -> bucket offsets; a second scan of ceil(count/S)
+//      -> segment offsets (a bucket with more than S entries is split, so a skewed
+//      witness -- most Filecoin scalars are 0/1 -- cannot serialise on one thread)
+//   3. counting-sort scatter of point indices (sign in bit 31) into bucket order
+//   4. bucket accumulation: one thread per segment, XYZZ accumulator, mixed-affine adds
+//      (8M + 2S each; INT32-multiply bound -- SURVEY §8d counts 10 Fq products per entry)
+//   5. bucket reduction: each thread running-sums a chunk of adjacent buckets of one
+//      window and lifts it by its chunk offset; a warp per window folds the chunks with
+//      register shuffles (warp-cooperative reduction)
+//   6. Horner over the windows (c doublings each), batch-free inversion, affine ABI bytes.
+// Results are canonical affine points, hence bit-exact whatever the summation order.
+#pragma once
+#include "common.cuh"
+#include "msm_digits.cuh"
+
+namespace b2 {
+
+#if defined(__CUDACC__)
+B2_D void load_scalar(const uint32_t* scalars, size_t i, uint32_t* s) {
+    const uint4* q = reinterpret_cast<const uint4*>(scalars + 8 * i);
+    uint4 a = __ldg(q), b = __ldg(q + 1);
+    s[0] = a.x; s[1] = a.y; s[2] = a.z; s[3] = a.w; s[4] = b.x; s[5] = b.y; s[6] = b.z; s[7] = b.w;
+}
+
+// ---- 1. histogram ------------------------------------------------------------------
+static __global__ void msm_hist_kernel(const uint32_t* __restrict__ scalars, size_t n, int c, int W, uint32_t* __restrict__ hist) {
+    const uint32_t B = 1u << (c - 1);
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        uint32_t s[8]; load_scalar(scalars, i, s);
+        for (int w = 0; w < W; ++w) {
+            int d = msm_signed_digit(s, w, c);
+            if (d) atomicAdd(hist + (size_t)w * B + (uint32_t)((d < 0 ? -d : d) - 1), 1u);
+        }
+    }
+}
+// ---- 3. scatter --------------------------------------------------------------------
+static __global__ void msm_scatter_kernel(const uint32_t* __restrict__ scalars, size_t n, int c, int W, uint32_t* __restrict__ cursor, uint32_t* __restrict__ sorted) {
+    const uint32_t B = 1u << (c - 1);
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        uint32_t s[8]; load_scalar(scalars, i, s);
+        for (int w = 0; w < W; ++w) {
+            int d = msm_signed_digit(s, w, c);
+            if (d) {
+                uint32_t slot = atomicAdd(cursor + (size_t)w * B + (uint32_t)((d < 0 ? -d : d) - 1), 1u);
+                sorted[slot] = (uint32_t)i | (d < 0 ? 0x80000000u : 0u);
+            }
+        }
+    }
+}
+// ---- 2. scans (uint32, exclusive, with the total appended at out[n]) -----------------
+constexpr int SCAN_BLOCK = 1024, SCAN_ITEMS = 8, SCAN_TILE = SCAN_BLOCK * SCAN_ITEMS;
+// mode 0: out = in ; mode 1: out = ceil(in / seg)
+static __global__ void __launch_bounds__(SCAN_BLOCK) scan_tile_kernel(const uint32_t* in, uint32_t* out, uint32_t* tile_sums, size_t n, int mode, uint32_t seg) {
+    __shared__ uint32_t warp_sums[32];
+    const size_t base = (size_t)blockIdx.x * SCAN_TILE + (size_t)threadIdx.x * SCAN_ITEMS;
+    uint32_t v[SCAN_ITEMS], sum = 0;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) {
+        uint32_t x = (base + k < n) ? in[base + k] : 0u;
+        if (mode == 1) x = (x + seg - 1) / seg;
+        v[k] = sum; sum += x;
+    }
+    uint32_t incl = sum;
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += t; }
+    if (lane == 31) warp_sums[wid] = incl;
+    __syncthreads();
+    if (wid == 0) {
+        uint32_t w = warp_sums[lane], wi = w;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { uint32_t t = __shfl_up_sync(0xffffffffu, wi, d); if (lane >= d) wi += t; }
+        warp_sums[lane] = wi - w;
+        if (lane == 31) tile_sums[blockIdx.x] = wi;
+    }
+    __syncthreads();
+    const uint32_t off = warp_sums[wid] + incl - sum;
+#pragma unroll
+    for (int k = 0; k < SCAN_ITEMS; ++k) if (base + k < n) out[base + k] = off + v[k];
+}
+static __global__ void __launch_bounds__(1024) scan_top_kernel(uint32_t* tile_sums, int n_tiles, uint32_t* total_out) {
+    // single block; n_tiles <= 1024 * 64
+    __shared__ uint32_t sh[1024];
+    const int per = (n_tiles + 1023) / 1024;
+    uint32_t sum = 0;
+    for (int k = 0; k < per; ++k) { int i = threadIdx.x * per + k; if (i < n_tiles) sum += tile_sums[i]; }
+    sh[threadIdx.x] = sum;
+    __syncthreads();
+    for (int d = 1; d < 1024; d <<= 1) {
+        uint32_t t = threadIdx.x >= d ? sh[threadIdx.x - d] : 0u;
+        __syncthreads();
+        sh[threadIdx.x] += t;
+        __syncthreads();
+    }
+    uint32_t run = sh[threadIdx.x] - sum;
+    for (int k = 0; k < per; ++k) { int i = threadIdx.x * per + k; if (i < n_tiles) { uint32_t x = tile_sums[i]; tile_sums[i] = run; run += x; } }
+    if (threadIdx.x == 1023) *total_out = sh[1023];
+}
+static __global__ void scan_add_kernel(uint32_t* out, const uint32_t* tile_sums, size_t n) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) out[i] += tile_sums[i / SCAN_TILE];
+}
+
+// ---- 4. bucket accumulation ----------------------------------------------------------
+template <class F> B2_D Affine<F> load_affine(const Affine<F>* p) {
+    Affine<F> r;
+    const uint4* q = reinterpret_cast<const uint4*>(p);
+    uint32_t* d = reinterpret_cast<uint32_t*>(&r);
+#pragma unroll
+    for (int i = 0; i < (int)(sizeof(Affine<F>) / 16); ++i) { uint4 t = __ldg(q + i); d[4 * i] = t.x; d[4 * i + 1] = t.y; d[4 * i + 2] = t.z; d[4 * i + 3] = t.w; }
+    return r;
+}
+template <class F, int THREADS> __global__ void __launch_bounds__(THREADS)
+msm_accumulate_kernel(const Affine<F>* __restrict__ bases, const uint32_t* __restrict__ sorted, const uint32_t* __restrict__ hist,
+                      const uint32_t* __restrict__ off, const uint32_t* __restrict__ seg_off, uint32_t n_buckets, uint32_t S, Xyzz<F>* __restrict__ seg_acc) {
+    const uint32_t seg_total = seg_off[n_buckets];
+    for (uint32_t seg = blockIdx.x * blockDim.x + threadIdx.x; seg < seg_total; seg += gridDim.x * blockDim.x) {
+        // bucket owning this segment: largest b with seg_off[b] <= seg
+        uint32_t lo = 0, hi = n_buckets;
+        while (hi - lo > 1) { uint32_t mid = (lo + hi) >> 1; if (seg_off[mid] <= seg) lo = mid; else hi = mid; }
+        const uint32_t b = lo;
+        const uint32_t begin = off[b] + (seg - seg_off[b]) * S;
+        const uint32_t bucket_end = off[b] + hist[b];
+        const uint32_t end = begin + S < bucket_end ? begin + S : bucket_end;
+        Xyzz<F> acc = Xyzz<F>::identity();
+        for (uint32_t e = begin; e < end; ++e) {
+            const uint32_t ix = sorted[e];
+            Affine<F> p = load_affine(bases + (ix & 0x7fffffffu));
+            if (ix >> 31) p.y = p.y.neg();
+            acc.add_mixed(p);
+        }
+        seg_acc[seg] = acc;
+    }
+}
+
+// ---- 5. bucket reduction -------------------------------------------------------------
+template <class F> __global__ void __launch_bounds__(128)
+msm_reduce_kernel(const Xyzz<F>* __restrict__ seg_acc, const uint32_t* __restrict__ seg_off, int c, int W, uint32_t T, Xyzz<F>* __restrict__ partial) {
+    const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= (uint32_t)W * T) return;
+    const uint32_t w = gid / T, t = gid % T, B = 1u << (c - 1), per = B / T;
+    const uint32_t lo = t * per;
+    Xyzz<F> run = Xyzz<F>::identity(), acc = Xyzz<F>::identity();
+    for (uint32_t j = lo + per; j-- > lo;) {                    // weights j+1, descending
+        const uint32_t b = w * B + j;
+        for (uint32_t s = seg_off[b]; s < seg_off[b + 1]; ++s) { Xyzz<F> t = seg_acc[s]; xyzz_add_call(&run, &t); }
+        xyzz_add_call(&acc, &run);
+    }
+    // acc = sum (j - lo + 1) B_j ;  add lo * run (double-and-add over the bits of lo)
+    Xyzz<F> m = Xyzz<F>::identity();
+    for (int bit = 31; bit >= 0; --bit) {
+        xyzz_dbl_call(&m);
+        if ((lo >> bit) & 1u) xyzz_add_call(&m, &run);
+    }
+    xyzz_add_call(&acc, &m);
+    partial[gid] = acc;
+}
+template <class F> B2_D Xyzz<F> xyzz_shfl_down(const Xyzz<F>& p, int delta) {
+    Xyzz<F> r;
+    const uint32_t* s = reinterpret_cast<const uint32_t*>(&p);
+    uint32_t* d = reinterpret_cast<uint32_t*>(&r);
+#pragma unroll
+    for (int i = 0; i < (int)(sizeof(Xyzz<F>) / 4); ++i) d[i] = __shfl_down_sync(0xffffffffu, s[i], delta);
+    return r;
+}
+// one warp per window: fold the T chunk results
+template <class F> __global__ void __launch_bounds__(32)
+msm_window_sum_kernel(const Xyzz<F>* __restrict__ partial, uint32_t T, Xyzz<F>* __restrict__ win) {
+    const uint32_t w = blockIdx.x, lane = threadIdx.x;
+    Xyzz<F> acc = Xyzz<F>::identity();
+    for (uint32_t i = lane; i < T; i += 32) { Xyzz<F> t = partial[w * T + i]; xyzz_add_call(&acc, &t); }
+    for (int d = 16; d >= 1; d >>= 1) {
+        Xyzz<F> o = xyzz_shfl_down(acc, d);
+        xyzz_add_call(&acc, &o);
+    }
+    if (lane == 0) win[w] = acc;
+}
+// ---- 6. Horner over windows + affine output --------------------------------------------
+B2_D void egress_fq(uint8_t* p, const Fq& m) {
+    Fq c; m.to_canonical(c.v);
+    uint32_t* q = reinterpret_cast<uint32_t*>(p);
+#pragma unroll
+    for (int i = 0; i < 12; ++i) q[i] = c.v[i];
+}
+B2_D void egress_affine(uint8_t* p, const G1Affine& a) { egress_fq(p, a.x); egress_fq(p + 48, a.y); }
+B2_D void egress_affine(uint8_t* p, const G2Affine& a) { egress_fq(p, a.x.c0); egress_fq(p + 48, a.x.c1); egress_fq(p + 96, a.y.c0); egress_fq(p + 144, a.y.c1); }
+
+template <class F> __global__ void __launch_bounds__(32)
+msm_final_kernel(const Xyzz<F>* __restrict__ win, int c, int W, uint8_t* __restrict__ out_bytes) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    Xyzz<F> acc = win[W - 1];
+    for (int w = W - 2; w >= 0; --w) {
+        for (int k = 0; k < c; ++k) xyzz_dbl_call(&acc);
+        Xyzz<F> t = win[w];
+        xyzz_add_call(&acc, &t);
+    }
+    Affine<F> aff; xyzz_to_affine_call(&aff, &acc);
+    egress_affine(out_bytes, aff);
+}
+// sum of n affine points (combining per-rank partial results), single thread
+template <class F> __global__ void __launch_bounds__(32)
+sum_points_kernel(const Affine<F>* __restrict__ pts, size_t n, uint8_t* __restrict__ out_bytes) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    Xyzz<F> acc = Xyzz<F>::identity();
+    for (size_t i = 0; i < n; ++i) { Affine<F> t = pts[i]; xyzz_add_mixed_call(&acc, &t); }
+    Affine<F> aff; xyzz_to_affine_call(&aff, &acc);
+    egress_affine(out_bytes, aff);
+}
+
+// ---- fixed-base multiples of the group generator (synthetic bases, Groth16 setup) -------
+// table[w * 255 + (d-1)] = d * 2^(8w) * G, affine, w < 32
+template <class F> __global__ void __launch_bounds__(32) fixed_base_roots_kernel(Affine<F> gen, Affine<F>* roots /*32*/) {
+    const int w = threadIdx.x;
+    Xyzz<F> p = Xyzz<F>::from_affine(gen);
+    for (int k = 0; k < 8 * w; ++k) xyzz_dbl_call(&p);
+    Affine<F> aff; xyzz_to_affine_call(&aff, &p);
+    roots[w] = aff;
+}
+template <class F> __global__ void __launch_bounds__(64) fixed_base_table_kernel(const Affine<F>* roots, Affine<F>* table) {
+    const int id = blockIdx.x * blockDim.x + threadIdx.x;
+    if (id >= 32 * 255) return;
+    const int w = id / 255, d = id % 255 + 1;
+    const Affine<F> base = roots[w];
+    Xyzz<F> p = Xyzz<F>::identity();
+    for (int bit = 7; bit >= 0; --bit) {
+        xyzz_dbl_call(&p);
+        if ((d >> bit) & 1) xyzz_add_mixed_call(&p, &base);
+    }
+    Affine<F> aff; xyzz_to_affine_call(&aff, &p);
+    table[id] = aff;
+}
+template <class F> __global__ void __launch_bounds__(128) gen_mul_kernel(const Affine<F>* __restrict__ table, const uint32_t* __restrict__ scalars, size_t n, Affine<F>* __restrict__ out) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        uint32_t s[8]; load_scalar(scalars, i, s);
+        Xyzz<F> acc = Xyzz<F>::identity();
+        for (int w = 0; w < 32; ++w) {
+            const uint32_t d = (s[w >> 2] >> (8 * (w & 3))) & 0xffu;
+            if (d) { Affine<F> t = load_affine(table + w * 255 + (d - 1)); xyzz_add_mixed_call(&acc, &t); }
+        }
+        Affine<F> aff; xyzz_to_affine_call(&aff, &acc);
+        out[i] = aff;
+    }
+}
+
+// ---- host driver ---------------------------------------------------------------------
+inline int msm_pick_window(size_t n) {
+    int lg = 0;
+    while (((size_t)1 << (lg + 1)) <= n) ++lg;
+    int c = lg - 4;
+    if (c < 8) c = 8;
+    if (c > 16) c = 16;
+    return c;
+}
+
+static void scan_u32(Ctx* ctx, cudaStream_t st, const uint32_t* in, uint32_t* out /*n+1*/, size_t n, int mode, uint32_t seg, uint32_t* tile_sums) {
+    const int n_tiles = (int)((n + SCAN_TILE - 1) / SCAN_TILE);
+    B2_REQUIRE(n_tiles <= 1024 * 64, B2G16_E_INVALID_ARG, "msm: too many buckets for the scan");
+    scan_tile_kernel<<<n_tiles, SCAN_BLOCK, 0, st>>>(in, out, tile_sums, n, mode, seg);
+    scan_top_kernel<<<1, 1024, 0, st>>>(tile_sums, n_tiles, out + n);
+    scan_add_kernel<<<grid_for(n, 256), 256, 0, st>>>(out, tile_sums, n);
+    ctx->launches += 3;
+    B2_CUDA(cudaGetLastError());
+}
+
+template <class F>
+void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size_t n, uint8_t* d_out_bytes, cudaStream_t st, int window_bits) {
+    constexpr int OUT_BYTES = (int)sizeof(Affine<F>);
+    if (n == 0) { B2_CUDA(cudaMemsetAsync(d_out_bytes, 0, OUT_BYTES, st)); return; }
+    B2_REQUIRE(n < ((size_t)1 << 31), B2G16_E_INVALID_ARG, "msm: at most 2^31-1 points per call");
+    int c = window_bits ? window_bits : (ctx->msm_window_override ? ctx->msm_window_override : msm_pick_window(n));
+    B2_REQUIRE(c >= 8 && c <= 20, B2G16_E_INVALID_ARG, "msm: window bits must be in [8, 20]");
+    const int W = msm_windows(c);
+    const uint32_t B = 1u << (c - 1);
+    const size_t nb = (size_t)W * B;
+    B2_REQUIRE((double)n * W < 4.0e9, B2G16_E_INVALID_ARG, "msm: n * windows exceeds 32-bit entry offsets");
+    const size_t max_entries = n * (size_t)W;
+    uint32_t mean = (uint32_t)(n >> (c - 1));
+    const uint32_t S = 4 * mean + 256;
+    const size_t max_segs = nb + max_entries / S + 1;
+    const int n_tiles = (int)((nb + SCAN_TILE - 1) / SCAN_TILE);
+
+    DevBuf<uint32_t> hist(nb + 1, st), off(nb + 1, st), cursor(nb + 1, st), seg_off(nb + 1, st), tile_sums((size_t)n_tiles + 1, st), sorted(max_entries, st);
+    DevBuf<Xyzz<F>> seg_acc(max_segs, st);
+    const uint32_t T = msm_reduce_chunks(c);
+    DevBuf<Xyzz<F>> partial((size_t)W * T, st), win(W, st);
+
+    cudaEvent_t ev[6] = {};
+    const bool timed = ctx->time_msm;
+    if (timed) for (auto& e : ev) B2_CUDA(cudaEventCreate(&e));
+    auto mark = [&](int i) { if (timed) B2_CUDA(cudaEventRecord(ev[i], st)); };
+
+    mark(0);
+    B2_CUDA(cudaMemsetAsync(hist.get(), 0, (nb + 1) * sizeof(uint32_t), st));
+    msm_hist_kernel<<<grid_for(n, 256, 148 * 8), 256, 0, st>>>(d_scalars, n, c, W, hist.get()); ctx->launches++;
+    mark(1);
+    scan_u32(ctx, st, hist.get(), off.get(), nb, 0, 1, tile_sums.get());
+    scan_u32(ctx, st, hist.get(), seg_off.get(), nb, 1, S, tile_sums.get());
+    B2_CUDA(cudaMemcpyAsync(cursor.get(), off.get(), (nb + 1) * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+    mark(2);
+    msm_scatter_kernel<<<grid_for(n, 256, 148 * 8), 256, 0, st>>>(d_scalars, n, c, W, cursor.get(), sorted.get()); ctx->launches++;
+    mark(3);
+    constexpr int ACC_THREADS = sizeof(F) > 48 ? 64 : 128;
+    msm_accumulate_kernel<F, ACC_THREADS><<<grid_for(max_segs, ACC_THREADS, 148 * 64), ACC_THREADS, 0, st>>>(
+        d_bases, sorted.get(), hist.get(), off.get(), seg_off.get(), (uint32_t)nb, S, seg_acc.get()); ctx->launches++;
+    mark(4);
+    msm_reduce_kernel<F><<<(W * T + 127) / 128, 128, 0, st>>>(seg_acc.get(), seg_off.get(), c, W, T, partial.get()); ctx->launches++;
+    msm_window_sum_kernel<F><<<W, 32, 0, st>>>(partial.get(), T, win.get()); ctx->launches++;
+    msm_final_kernel<F><<<1, 32, 0, st>>>(win.get(), c, W, d_out_bytes); ctx->launches++;
+    mark(5);
+    B2_CUDA(cudaGetLastError());
+    if (timed) {
+        B2_CUDA(cudaEventSynchronize(ev[5]));
+        for (int i = 0; i < 5; ++i) B2_CUDA(cudaEventElapsedTime(&ctx->msm_ms[i], ev[i], ev[i + 1]));
+        for (auto& e : ev) cudaEventDestroy(e);
+    }
+}
+
+template <class F>
+Affine<F>* fixed_base_table(Ctx* ctx, int slot, const Affine<F>& gen) {
+    if (ctx->fixed_base[slot]) return (Affine<F>*)ctx->fixed_base[slot];
+    Affine<F>* table = nullptr;
+    B2_CUDA(cudaMalloc((void**)&table, sizeof(Affine<F>) * (32 * 255 + 32)));
+    Affine<F>* roots = table + 32 * 255;
+    fixed_base_roots_kernel<F><<<1, 32, 0, ctx->stream>>>(gen, roots);
+    fixed_base_table_kernel<F><<<(32 * 255 + 63) / 64, 64, 0, ctx->stream>>>(roots, table);
+    ctx->launches += 2;
+    B2_CUDA(cudaGetLastError());
+    ctx->fixed_base[slot] = table;
+    return table;
+}
+#endif  // __CUDACC__
+
+}  // namespace b2

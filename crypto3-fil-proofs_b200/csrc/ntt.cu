@@ -1,0 +1,142 @@
+// Fr evaluation-domain transforms on the device: domain tables, the natural-order
+// fft / inverse_fft / coset API and the r1cs_to_qap witness-map tail (H polynomial).
+// Replaces crypto3-math `evaluation_domain<Fr>` and zk `r1cs_to_qap::witness_map`
+// (un-vendored); called on behalf of compound_proof::circuit_proofs
+// (libs/storage/include/nil/filecoin/storage/proofs/core/proof/compound_proof.hpp:127-137).
+#include "common.cuh"
+#include "ntt_plan.cuh"
+
+namespace b2 {
+
+struct NttDomain {
+    int log_n = 0;
+    NttPlan plan;
+    Fr *tlo_f = nullptr, *thi_f = nullptr, *tlo_i = nullptr, *thi_i = nullptr;   // w^e, w^-e
+    Fr *glo_f = nullptr, *ghi_f = nullptr, *glo_i = nullptr, *ghi_i = nullptr;   // g^e, n^-1 g^-e
+    Fr n_inv, zinv;                 // n^-1 ;  (g^n - 1)^-1
+};
+
+// out[e] = pre * base^(e << shift)
+__global__ void pow_table_kernel(Fr* out, Fr base, Fr pre, int shift, uint32_t count) {
+    for (uint32_t e = blockIdx.x * blockDim.x + threadIdx.x; e < count; e += gridDim.x * blockDim.x) {
+        uint64_t x = (uint64_t)e << shift;
+        Fr r = pre, b = base;
+        while (x) { if (x & 1) r = r * b; b = b.sqr(); x >>= 1; }
+        fr_store(out + e, r);
+    }
+}
+
+static Fr host_fr_u64(uint64_t x) {
+    uint32_t c[8] = {(uint32_t)x, (uint32_t)(x >> 32), 0, 0, 0, 0, 0, 0};
+    return Fr::from_canonical(c);
+}
+static Fr host_pow_u64(Fr b, uint64_t e) {
+    Fr r = Fr::one();
+    while (e) { if (e & 1) r = r * b; b = b.sqr(); e >>= 1; }
+    return r;
+}
+// 7^((r-1) >> log_n): primitive 2^log_n-th root of unity
+Fr host_root_of_unity(int log_n) {
+    uint32_t e[8];
+    for (int i = 0; i < 8; ++i) e[i] = FrParams::P(i);
+    e[0] -= 1;                                         // r - 1 (r is odd, no borrow)
+    for (int s = 0; s < log_n; ++s)
+        for (int i = 0; i < 8; ++i) e[i] = (e[i] >> 1) | (i < 7 ? e[i + 1] << 31 : 0);
+    return host_fr_u64(7).pow_limbs(e, 8);
+}
+
+static Fr* make_table(Ctx* c, Fr base, Fr pre, int shift, uint32_t count) {
+    Fr* d = nullptr;
+    B2_CUDA(cudaMalloc((void**)&d, (size_t)count * sizeof(Fr)));
+    pow_table_kernel<<<grid_for(count, 256), 256, 0, c->stream>>>(d, base, pre, shift, count);
+    c->launches++;
+    B2_CUDA(cudaGetLastError());
+    return d;
+}
+
+void ntt_init_roots(Ctx* c) {
+    if (c->roots_fwd) return;
+    Fr w = host_root_of_unity(NTT_ROOT_LOG);
+    c->roots_fwd = make_table(c, w, Fr::one(), 0, 1u << (NTT_ROOT_LOG - 1));
+    c->roots_inv = make_table(c, w.inv(), Fr::one(), 0, 1u << (NTT_ROOT_LOG - 1));
+    B2_CUDA(cudaFuncSetAttribute(ntt_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * sizeof(uint4) << NTT_TILE_LOG));
+}
+
+NttDomain* ntt_domain(Ctx* c, int log_n) {
+    auto it = c->domains.find(log_n);
+    if (it != c->domains.end()) return it->second;
+    B2_REQUIRE(log_n >= 0 && log_n <= 30, B2G16_E_INVALID_ARG, "domain size must be 2^0..2^30");
+    ntt_init_roots(c);
+    NttDomain* d = new NttDomain();
+    d->log_n = log_n;
+    d->plan = ntt_make_plan(log_n);
+    const int lo = d->plan.lo_bits, hi = log_n - lo;
+    const uint32_t n_lo = 1u << lo, n_hi = 1u << (hi > 0 ? hi : 0);
+    Fr w = host_root_of_unity(log_n), wi = w.inv();
+    Fr g = host_fr_u64(7), gi = g.inv();
+    d->n_inv = host_fr_u64(1ull << log_n).inv();
+    d->zinv = (host_pow_u64(g, 1ull << log_n) - Fr::one()).inv();
+    d->tlo_f = make_table(c, w, Fr::one(), 0, n_lo);  d->thi_f = make_table(c, w, Fr::one(), lo, n_hi);
+    d->tlo_i = make_table(c, wi, Fr::one(), 0, n_lo); d->thi_i = make_table(c, wi, Fr::one(), lo, n_hi);
+    d->glo_f = make_table(c, g, Fr::one(), 0, n_lo);  d->ghi_f = make_table(c, g, Fr::one(), lo, n_hi);
+    d->glo_i = make_table(c, gi, d->n_inv, 0, n_lo);  d->ghi_i = make_table(c, gi, Fr::one(), lo, n_hi);
+    c->domains[log_n] = d;
+    return d;
+}
+
+void ntt_free_domains(Ctx* c) {
+    for (auto& kv : c->domains) {
+        NttDomain* d = kv.second;
+        Fr* t[8] = {d->tlo_f, d->thi_f, d->tlo_i, d->thi_i, d->glo_f, d->ghi_f, d->glo_i, d->ghi_i};
+        for (Fr* p : t) cudaFree(p);
+        delete d;
+    }
+    c->domains.clear();
+    cudaFree(c->roots_fwd); cudaFree(c->roots_inv);
+    c->roots_fwd = c->roots_inv = nullptr;
+}
+
+static NttTables tables(Ctx* c, const NttDomain* d, bool inverse) {
+    NttTables t;
+    t.roots = inverse ? c->roots_inv : c->roots_fwd;
+    t.tlo = inverse ? d->tlo_i : d->tlo_f; t.thi = inverse ? d->thi_i : d->thi_f;
+    t.glo = inverse ? d->glo_i : d->glo_f; t.ghi = inverse ? d->ghi_i : d->ghi_f;
+    return t;
+}
+
+static void launch_pass(Ctx* c, const Fr* src, Fr* dst, const NttPass& p) {
+    const uint64_t tiles = ntt_pass_tiles(p);
+    const int T = 1 << (p.k + p.logc);
+    const size_t smem = 2 * sizeof(uint4) * (size_t)T;
+    const int max_grid = 148 * 3 * 4;                      // 3 resident CTAs per SM, a few waves
+    int grid = (int)(tiles < (uint64_t)max_grid ? tiles : (uint64_t)max_grid);
+    int block = T / 2 < 256 ? (T / 2 < 32 ? 32 : T / 2) : 256;
+    ntt_pass_kernel<<<grid, block, smem, c->stream>>>(src, dst, p);
+    c->launches++;
+    B2_CUDA(cudaGetLastError());
+}
+
+void ntt_natural_ex(Ctx* c, const Fr* src, Fr* dst, Fr* tmp, int log_n, bool inverse, bool coset,
+                    bool in_canon, bool out_canon, int* d_bad) {
+    NttDomain* d = ntt_domain(c, log_n);
+    NttConsts k{d->n_inv, d->zinv};
+    for (auto& s : ntt_steps_natural(d->plan, tables(c, d, inverse), k, src, dst, tmp, inverse, coset, in_canon, out_canon, d_bad))
+        launch_pass(c, s.src, s.dst, s.pass);
+}
+
+bool ntt_needs_tmp(int log_n) { return ntt_make_plan(log_n).digits.n_pass > 1; }
+
+void ntt_natural(Ctx* c, Fr* d_data, int log_n, bool inverse, bool coset) {
+    DevBuf<Fr> tmp;
+    if (ntt_needs_tmp(log_n)) tmp.alloc((size_t)1 << log_n, c->stream);
+    ntt_natural_ex(c, d_data, d_data, tmp.get(), log_n, inverse, coset, false, false, nullptr);
+}
+
+void h_from_abc_dev(Ctx* c, Fr* d_a, Fr* d_b, Fr* d_c, int log_m, uint32_t* d_h_canonical, bool in_canon, int* d_bad) {
+    NttDomain* d = ntt_domain(c, log_m);
+    NttConsts k{d->n_inv, d->zinv};
+    for (auto& s : ntt_steps_h(d->plan, tables(c, d, false), tables(c, d, true), k, d_a, d_b, d_c, reinterpret_cast<Fr*>(d_h_canonical), in_canon, d_bad))
+        launch_pass(c, s.src, s.dst, s.pass);
+}
+
+}  // namespace b2

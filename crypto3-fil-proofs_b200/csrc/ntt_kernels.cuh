@@ -61,6 +61,13 @@ struct NttPass {
     const Fr* glo; const Fr* ghi; int g_lo_bits;    // scale(e) = glo[e & mask] * ghi[e >> g_lo_bits]
     Fr cscale;
     NttDigits digits;
+    // fusions at the two ends of a transform chain
+    int in_canon;               // input holds canonical 32-byte scalars: convert (x * R^2) on load
+    int out_canon;              // write canonical scalars on store
+    int perm_store;             // store position pos -> ntt_digit_index(digits, pos) (digit-reversed -> natural)
+    int fuse_abc;               // load computes (x * b[pos] - c[pos]) * zinv   (witness map)
+    const Fr* src_b; const Fr* src_c; Fr zinv;
+    int* bad;                   // device flag, set when an in_canon input is >= r (device build only)
 };
 
 struct Fr2x { uint4 lo, hi; };
@@ -138,6 +145,13 @@ B2_HD void ntt_phase_load(const NttPass& p, const NttTile& t, const Fr* data, ui
     int row = t.row_of(e), col = t.col_of(e);
     uint64_t g = t.gpos(row, col);
     Fr x = fr_load(data + g);
+    if (p.in_canon) {
+#if defined(__CUDA_ARCH__)
+        if (Fr::geq_p(x.v)) atomicOr(p.bad, 1);
+#endif
+        x = x * Fr::r2();
+    }
+    if (p.fuse_abc) x = (x * fr_load(p.src_b + g) - fr_load(p.src_c + g)) * p.zinv;
     if (p.scale_mode == 1) x = x * ntt_scale(p, g);
     if (p.tw_mode == 2 && row != 0) x = x * ntt_twiddle(p, t.col0 + col, (uint32_t)row);
     fr_to_planes(x, s_lo[e], s_hi[e]);
@@ -166,18 +180,19 @@ B2_HD void ntt_phase_store(const NttPass& p, const NttTile& t, Fr* data, const u
     uint64_t g = t.gpos(row, col);
     if (p.tw_mode == 1 && row != 0) x = x * ntt_twiddle(p, t.col0 + col, (uint32_t)row);
     if (p.scale_mode == 2) x = x * ntt_scale(p, g);
-    fr_store(data + g, x);
+    if (p.out_canon) { Fr c; x.to_canonical(c.v); x = c; }
+    fr_store(data + (p.perm_store ? ntt_digit_index(p.digits, g) : g), x);
 }
 
 #if defined(__CUDACC__)
-__global__ void __launch_bounds__(256) ntt_pass_kernel(Fr* data, const NttPass p) {
+static __global__ void __launch_bounds__(256) ntt_pass_kernel(const Fr* src, Fr* data, const NttPass p) {
     extern __shared__ uint4 smem[];
     const int T = 1 << (p.k + p.logc);
     uint4* s_lo = smem;
     uint4* s_hi = smem + T;
     for (uint64_t tile_id = blockIdx.x; tile_id < ((1ull << p.log_n) >> (p.k + p.logc)); tile_id += gridDim.x) {
         const NttTile t = ntt_make_tile(p, tile_id);
-        for (int e = threadIdx.x; e < T; e += blockDim.x) ntt_phase_load(p, t, data, s_lo, s_hi, e);
+        for (int e = threadIdx.x; e < T; e += blockDim.x) ntt_phase_load(p, t, src, s_lo, s_hi, e);
         __syncthreads();
         for (int hs = p.k - 1; hs >= 0; --hs) {
             for (int b = threadIdx.x; b < T / 2; b += blockDim.x) ntt_phase_stage(p, t, s_lo, s_hi, hs, b);
@@ -189,7 +204,7 @@ __global__ void __launch_bounds__(256) ntt_pass_kernel(Fr* data, const NttPass p
 }
 
 // out[digit_index(pos)] = in[pos]  (digit-reversed -> natural), or the inverse gather
-__global__ void ntt_permute_kernel(const Fr* in, Fr* out, NttDigits d, int to_natural) {
+static __global__ void ntt_permute_kernel(const Fr* in, Fr* out, NttDigits d, int to_natural) {
     uint64_t n = 1ull << d.log_n;
     for (uint64_t pos = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; pos < n; pos += (uint64_t)gridDim.x * blockDim.x) {
         uint64_t idx = ntt_digit_index(d, pos);

@@ -48,3 +48,136 @@ int emu_fq_op(int op, const uint8_t* a, const uint8_t* b, size_t n, uint8_t* out
 int emu_g1_sum(int mode, const uint8_t* p, size_t n, uint8_t* out) { return sum_points<Fq, 96>(mode, p, n, out); }
 int emu_g2_sum(int mode, const uint8_t* p, size_t n, uint8_t* out) { return sum_points<Fq2, 192>(mode, p, n, out); }
 }
+
+// ---------------------------------------------------------------------------------------
+// NTT: the device pass kernel body (ntt_kernels.cuh phases) and the chain builders
+// (ntt_plan.cuh) executed tile by tile on the CPU, tables built with the same formulas as
+// ntt.cu.  Checks plan / tile / twiddle index arithmetic against the oracle without a GPU.
+#include <vector>
+#include "ntt_plan.cuh"
+#include "msm_digits.cuh"
+
+static Fr fr_u64(uint64_t x) { uint32_t c[8] = {(uint32_t)x, (uint32_t)(x >> 32), 0, 0, 0, 0, 0, 0}; return Fr::from_canonical(c); }
+static Fr fr_pow(Fr b, uint64_t e) { Fr r = Fr::one(); while (e) { if (e & 1) r = r * b; b = b.sqr(); e >>= 1; } return r; }
+static Fr root_of_unity(int log_n) {
+    uint32_t e[8];
+    for (int i = 0; i < 8; ++i) e[i] = FrParams::P(i);
+    e[0] -= 1;
+    for (int s = 0; s < log_n; ++s) for (int i = 0; i < 8; ++i) e[i] = (e[i] >> 1) | (i < 7 ? e[i + 1] << 31 : 0);
+    return fr_u64(7).pow_limbs(e, 8);
+}
+static std::vector<Fr> pow_table(Fr base, Fr pre, int shift, uint32_t count) {
+    std::vector<Fr> t(count);
+    for (uint32_t e = 0; e < count; ++e) t[e] = pre * fr_pow(base, (uint64_t)e << shift);
+    return t;
+}
+struct EmuDomain {
+    NttPlan plan; NttConsts k;
+    std::vector<Fr> roots_f, roots_i, tlo_f, thi_f, tlo_i, thi_i, glo_f, ghi_f, glo_i, ghi_i;
+    explicit EmuDomain(int log_n) {
+        plan = ntt_make_plan(log_n);
+        int lo = plan.lo_bits, hi = log_n - lo;
+        uint32_t n_lo = 1u << lo, n_hi = 1u << (hi > 0 ? hi : 0);
+        Fr w = root_of_unity(log_n), wi = w.inv(), g = fr_u64(7), gi = g.inv();
+        k.n_inv = fr_u64(1ull << log_n).inv();
+        k.zinv = (fr_pow(g, 1ull << log_n) - Fr::one()).inv();
+        Fr w11 = root_of_unity(NTT_ROOT_LOG);
+        roots_f = pow_table(w11, Fr::one(), 0, 1u << (NTT_ROOT_LOG - 1));
+        roots_i = pow_table(w11.inv(), Fr::one(), 0, 1u << (NTT_ROOT_LOG - 1));
+        tlo_f = pow_table(w, Fr::one(), 0, n_lo); thi_f = pow_table(w, Fr::one(), lo, n_hi);
+        tlo_i = pow_table(wi, Fr::one(), 0, n_lo); thi_i = pow_table(wi, Fr::one(), lo, n_hi);
+        glo_f = pow_table(g, Fr::one(), 0, n_lo); ghi_f = pow_table(g, Fr::one(), lo, n_hi);
+        glo_i = pow_table(gi, k.n_inv, 0, n_lo); ghi_i = pow_table(gi, Fr::one(), lo, n_hi);
+    }
+    NttTables tables(bool inverse) const {
+        NttTables t;
+        t.roots = (inverse ? roots_i : roots_f).data();
+        t.tlo = (inverse ? tlo_i : tlo_f).data(); t.thi = (inverse ? thi_i : thi_f).data();
+        t.glo = (inverse ? glo_i : glo_f).data(); t.ghi = (inverse ? ghi_i : ghi_f).data();
+        return t;
+    }
+};
+static void run_step(const NttStep& s) {
+    const NttPass& p = s.pass;
+    const int T = 1 << (p.k + p.logc);
+    std::vector<uint4> lo(T), hi(T);
+    for (uint64_t tile = 0; tile < ntt_pass_tiles(p); ++tile) {
+        NttTile t = ntt_make_tile(p, tile);
+        for (int e = 0; e < T; ++e) ntt_phase_load(p, t, s.src, lo.data(), hi.data(), e);
+        for (int hs = p.k - 1; hs >= 0; --hs) for (int b = 0; b < T / 2; ++b) ntt_phase_stage(p, t, lo.data(), hi.data(), hs, b);
+        for (int e = 0; e < T; ++e) ntt_phase_store(p, t, s.dst, lo.data(), hi.data(), e);
+    }
+}
+extern "C" {
+int emu_ntt(uint8_t* data, unsigned log_n, int inverse, int coset) {
+    EmuDomain d((int)log_n);
+    size_t n = (size_t)1 << log_n;
+    std::vector<Fr> buf(n), tmp(n);
+    memcpy(buf.data(), data, 32 * n);
+    for (auto& s : ntt_steps_natural(d.plan, d.tables(inverse != 0), d.k, buf.data(), buf.data(), tmp.data(), inverse != 0, coset != 0, true, true, nullptr)) run_step(s);
+    memcpy(data, buf.data(), 32 * n);
+    return d.plan.digits.n_pass;
+}
+int emu_h_from_abc(const uint8_t* a, const uint8_t* b, const uint8_t* c, unsigned log_m, uint8_t* h) {
+    EmuDomain d((int)log_m);
+    size_t m = (size_t)1 << log_m;
+    std::vector<Fr> va(m), vb(m), vc(m), vh(m);
+    memcpy(va.data(), a, 32 * m); memcpy(vb.data(), b, 32 * m); memcpy(vc.data(), c, 32 * m);
+    for (auto& s : ntt_steps_h(d.plan, d.tables(false), d.tables(true), d.k, va.data(), vb.data(), vc.data(), vh.data(), true, nullptr)) run_step(s);
+    memcpy(h, vh.data(), 32 * m);
+    return 0;
+}
+// signed digits of one canonical scalar: out[w], w < msm_windows(c)
+int emu_msm_digits(const uint8_t* scalar, int c, int* out) {
+    uint32_t s[8]; memcpy(s, scalar, 32);
+    int W = msm_windows(c);
+    for (int w = 0; w < W; ++w) out[w] = msm_signed_digit(s, w, c);
+    return W;
+}
+// The MSM pipeline of msm_impl.cuh restated sequentially with the same bucket layout,
+// segment split, chunked running sum (+ chunk-offset lift) and Horner tail.
+int emu_msm_g1(const uint8_t* bases, const uint8_t* scalars, size_t n, int c, uint32_t S, uint8_t* out) {
+    const int W = msm_windows(c);
+    const uint32_t B = 1u << (c - 1), T = msm_reduce_chunks(c), per = B / T;
+    std::vector<G1Affine> pts(n);
+    for (size_t i = 0; i < n; ++i) if (!load(pts[i], bases + 96 * i)) return -2;
+    std::vector<std::vector<uint32_t>> bucket((size_t)W * B);
+    for (size_t i = 0; i < n; ++i) {
+        uint32_t s[8]; memcpy(s, scalars + 32 * i, 32);
+        for (int w = 0; w < W; ++w) {
+            int d = msm_signed_digit(s, w, c);
+            if (d) bucket[(size_t)w * B + (uint32_t)((d < 0 ? -d : d) - 1)].push_back((uint32_t)i | (d < 0 ? 0x80000000u : 0u));
+        }
+    }
+    std::vector<G1Xyzz> win(W);
+    for (int w = 0; w < W; ++w) {
+        G1Xyzz wsum = G1Xyzz::identity();
+        for (uint32_t t = 0; t < T; ++t) {
+            uint32_t lo = t * per;
+            G1Xyzz run = G1Xyzz::identity(), acc = G1Xyzz::identity();
+            for (uint32_t j = lo + per; j-- > lo;) {
+                const std::vector<uint32_t>& e = bucket[(size_t)w * B + j];
+                for (size_t s0 = 0; s0 < e.size(); s0 += S) {                 // segments
+                    G1Xyzz seg = G1Xyzz::identity();
+                    for (size_t q = s0; q < e.size() && q < s0 + S; ++q) {
+                        G1Affine p = pts[e[q] & 0x7fffffffu];
+                        if (e[q] >> 31) p.y = p.y.neg();
+                        seg.add_mixed(p);
+                    }
+                    run.add(seg);
+                }
+                acc.add(run);
+            }
+            G1Xyzz m = G1Xyzz::identity();
+            for (int bit = 31; bit >= 0; --bit) { m = m.dbl(); if ((lo >> bit) & 1u) m.add(run); }
+            acc.add(m);
+            wsum.add(acc);
+        }
+        win[w] = wsum;
+    }
+    G1Xyzz acc = win[W - 1];
+    for (int w = W - 2; w >= 0; --w) { for (int k = 0; k < c; ++k) acc = acc.dbl(); acc.add(win[w]); }
+    store(acc.to_affine(), out);
+    return 0;
+}
+}

@@ -116,3 +116,89 @@ def test_curve_ops_vs_oracle(emu, oracle):
         pm = np.stack([pts[0], gen(negk)[0]])
         getattr(emu, fn)(0, _p(pm), C.c_size_t(2), _p(out))
         assert not out.any()
+
+
+# ---- NTT pass kernels and MSM pipeline logic, executed on the CPU ------------------------
+def _deps_all():
+    return [SRC] + [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cuh")]
+
+
+@pytest.fixture(scope="module")
+def emu2():
+    os.makedirs(os.path.dirname(SO), exist_ok=True)
+    deps = _deps_all()
+    if not os.path.exists(SO) or any(os.path.getmtime(d) > os.path.getmtime(SO) for d in deps):
+        subprocess.check_call(["g++", "-O2", "-std=c++17", "-shared", "-fPIC", "-x", "c++", "-I", CSRC, SRC, "-o", SO])
+    return C.CDLL(SO)
+
+
+@pytest.mark.parametrize("log_n", [0, 1, 2, 5, 11, 12, 13, 14])
+@pytest.mark.parametrize("inverse,coset", [(0, 0), (1, 0), (0, 1), (1, 1)])
+def test_ntt_passes_vs_oracle(emu2, oracle, log_n, inverse, coset):
+    rng = np.random.Generator(np.random.PCG64(1000 + log_n))
+    x = codec.random_fr(1 << log_n, rng)
+    got = x.copy()
+    n_pass = emu2.emu_ntt(_p(got), C.c_uint(log_n), inverse, coset)
+    assert n_pass == (1 if log_n <= 11 else 2)
+    want = oracle.ntt(x, inverse=bool(inverse), coset=bool(coset))
+    assert np.array_equal(got, want)
+
+
+def test_ntt_golden(emu2):
+    g = util.golden("ntt")
+    checked = 0
+    for key in g.files:
+        if not key.startswith("in_"):
+            continue
+        log_n = int(key.split("_")[1])
+        for inv in (0, 1):
+            for cos in (0, 1):
+                got = g[key].copy()
+                emu2.emu_ntt(_p(got), C.c_uint(log_n), inv, cos)
+                assert np.array_equal(got, g[f"out_{log_n}_{inv}{cos}"]), (log_n, inv, cos)
+                checked += 1
+    assert checked >= 8
+
+
+@pytest.mark.parametrize("log_m", [1, 4, 11, 13])
+def test_h_chain_vs_oracle(emu2, oracle, log_m):
+    rng = np.random.Generator(np.random.PCG64(2000 + log_m))
+    m = 1 << log_m
+    # a*b - c must vanish on the domain for H to be a polynomial: take c = a*b pointwise
+    a, b = codec.random_fr(m, rng), codec.random_fr(m, rng)
+    c = oracle.field_op("fr", "mul", a, b)
+    want = oracle.h_from_abc(a, b, c)
+    got = np.zeros((m, 32), dtype=np.uint8)
+    assert emu2.emu_h_from_abc(_p(a), _p(b), _p(c), C.c_uint(log_m), _p(got)) == 0
+    assert np.array_equal(got, want)
+    assert not got[m - 1].any()
+
+
+@pytest.mark.parametrize("c", [8, 11, 13, 16, 20])
+def test_msm_signed_digits(emu2, c):
+    rng = np.random.Generator(np.random.PCG64(c))
+    vals = codec.fr_to_ints(codec.random_fr(200, rng)) + [0, 1, codec.R_MOD - 1, 2**c - 1, 2**(c - 1), 2**(c - 1) + 1, 2**254]
+    for v in vals:
+        out = (C.c_int * 64)()
+        s = np.frombuffer(int(v).to_bytes(32, "little"), dtype=np.uint8).copy()
+        W = emu2.emu_msm_digits(_p(s), c, out)
+        assert W == -(-256 // c)
+        ds = list(out[:W])
+        assert all(-(1 << (c - 1)) <= d <= (1 << (c - 1)) for d in ds)
+        assert sum(d << (c * w) for w, d in enumerate(ds)) == v
+
+
+@pytest.mark.parametrize("n,c,S", [(1, 8, 4), (37, 8, 4), (300, 9, 3), (300, 11, 1000)])
+def test_msm_pipeline_logic_vs_oracle(emu2, oracle, n, c, S):
+    rng = np.random.Generator(np.random.PCG64(n * 31 + c))
+    bases = oracle.g1_gen_mul(codec.random_fr(n, rng))
+    scal = codec.random_fr(n, rng)
+    scal[0] = 0
+    if n > 4:
+        scal[1] = 0; scal[1, 0] = 1                       # scalar 1
+        scal[2] = np.frombuffer((codec.R_MOD - 1).to_bytes(32, "little"), dtype=np.uint8)
+        bases[3] = 0                                       # identity base
+        bases[4] = bases[5]; scal[4] = scal[5]             # duplicate -> doubling branch inside a bucket
+    out = np.zeros(96, dtype=np.uint8)
+    assert emu2.emu_msm_g1(_p(bases), _p(scal), C.c_size_t(n), c, C.c_uint32(S), _p(out)) == 0
+    assert np.array_equal(out, oracle.msm_g1(bases, scal))
