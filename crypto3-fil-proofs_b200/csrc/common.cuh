@@ -90,6 +90,7 @@ void ntt_natural_ex(Ctx* c, const Fr* src, Fr* dst, Fr* tmp, int log_n, bool inv
                     bool in_canon, bool out_canon, int* d_bad);
 void ntt_natural(Ctx* c, Fr* d_data, int log_n, bool inverse, bool coset);
 bool ntt_needs_tmp(int log_n);
+Fr host_root_of_unity(int log_n);
 // witness-map chain: a,b,c evaluations (natural order; destroyed) -> H coefficients written
 // to d_h_canonical as canonical 32-byte scalars in natural order.
 void h_from_abc_dev(Ctx* c, Fr* d_a, Fr* d_b, Fr* d_c, int log_m, uint32_t* d_h_canonical, bool in_canon, int* d_bad);

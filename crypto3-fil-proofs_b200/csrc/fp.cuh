@@ -19,9 +19,18 @@
 #if defined(__CUDACC__)
 #define B2_HD __host__ __device__ __forceinline__
 #define B2_D __device__ __forceinline__
+// the field product: inlined into device code, an ordinary call in host code (the host
+// passes emulate the carry chain instruction by instruction; inlining 10+ of them per
+// group operation only costs compile time)
+#if defined(__CUDA_ARCH__)
+#define B2_HD_MUL __host__ __device__ __forceinline__
+#else
+#define B2_HD_MUL __host__ __device__ __attribute__((noinline))
+#endif
 #else
 #define B2_HD inline
 #define B2_D inline
+#define B2_HD_MUL inline
 #endif
 
 #if !defined(__CUDACC__)
@@ -250,7 +259,7 @@ template <class PR> struct alignas(16) Fp {
 
     // Montgomery product (CIOS, 32-bit limbs, even/odd 64-bit columns; the classic
     // carry-chain layout of GPU big-number code): N^2 + N^2 wide MADs + N low MULs.
-    B2_HD Fp operator*(const Fp& o) const {
+    B2_HD_MUL Fp operator*(const Fp& o) const {
         static_assert(N % 2 == 0, "even limb count");
         uint32_t ev[N], od[N], mod[N], a[N], b[N];
 #pragma unroll

@@ -1,0 +1,517 @@
+// Groth16 (r1cs_gg_ppzksnark, BLS12-381) prover on the device-resident proving key.
+// Stands where compound_proof::circuit_proofs
+// (libs/storage/include/nil/filecoin/storage/proofs/core/proof/compound_proof.hpp:127-137)
+// calls crypto3-zk `prove<r1cs_gg_ppzksnark<bls12<381>>>(pk, primary, aux)` for
+// seal_commit_phase2 (libs/filecoin/include/nil/filecoin/proofs/api/seal.hpp:298-308) and
+// generate_{winning,window}_post (.../api/post.hpp:225,345).  Algorithm: SURVEY App. B.
+//   device: ingest z -> a,b,c = A z, B z, C z (CSR SpMV, + input-consistency rows)
+//           -> 7 NTTs (H coefficients) -> 5 MSMs (A, B1, B2, L over z; H over h)
+//   host:   A = alpha + A' + r delta ; B = beta + B' + s delta ; C = H' + L' + sA + rB1 - rs delta
+//           -> 192-byte compressed proof (F/constants.hpp:93 SINGLE_PARTITION_PROOF_LEN)
+// The key layout mirrors scheme_params (S/core/crypto/scheme_params.hpp:38-67), dense.
+#include <cstring>
+#include <vector>
+#include "msm_impl.cuh"
+#include "api_util.cuh"
+#include "ntt_kernels.cuh"
+
+namespace b2 {
+
+struct DevCsr { uint64_t n_rows = 0, nnz = 0; uint32_t* row_ptr = nullptr; uint32_t* col = nullptr; Fr* val = nullptr; };
+
+}  // namespace b2
+
+struct b2g16_pk {
+    uint32_t log_m = 0;
+    uint64_t n_cons = 0, n_in = 0, n_aux = 0, n_vars = 0, m = 0;
+    b2::DevCsr A, B, C;
+    b2::G1Affine *a = nullptr, *b_g1 = nullptr, *l = nullptr, *h = nullptr;
+    b2::G2Affine* b_g2 = nullptr;
+    b2::G1Affine alpha_g1, beta_g1, delta_g1;     // host copies, Montgomery
+    b2::G2Affine beta_g2, delta_g2;
+};
+
+namespace b2 {
+
+// ------------------------------------------------------------------------------ kernels
+// a,b,c evaluations on the domain; rows >= n_cons of A carry the inputs
+__global__ void __launch_bounds__(256) abc_spmv_kernel(DevCsr A, DevCsr B, DevCsr C, const Fr* __restrict__ z, uint64_t n_cons, uint64_t n_in, uint64_t m,
+                                                       Fr* __restrict__ a, Fr* __restrict__ b, Fr* __restrict__ c) {
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < m; i += (uint64_t)gridDim.x * blockDim.x) {
+        Fr sa = Fr::zero(), sb = Fr::zero(), sc = Fr::zero();
+        if (i < n_cons) {
+            for (uint32_t k = A.row_ptr[i]; k < A.row_ptr[i + 1]; ++k) sa = sa + fr_load(A.val + k) * fr_load(z + A.col[k]);
+            for (uint32_t k = B.row_ptr[i]; k < B.row_ptr[i + 1]; ++k) sb = sb + fr_load(B.val + k) * fr_load(z + B.col[k]);
+            for (uint32_t k = C.row_ptr[i]; k < C.row_ptr[i + 1]; ++k) sc = sc + fr_load(C.val + k) * fr_load(z + C.col[k]);
+        } else if (i - n_cons <= n_in) {
+            sa = fr_load(z + (i - n_cons));
+        }
+        fr_store(a + i, sa); fr_store(b + i, sb); fr_store(c + i, sc);
+    }
+}
+// one layer of the forward-built synthetic instance: z[out0 + i] = (A_i . z)(B_i . z), rows [r0, r1)
+__global__ void __launch_bounds__(256) synth_layer_kernel(DevCsr A, DevCsr B, Fr* __restrict__ z, uint64_t r0, uint64_t r1, uint64_t out0) {
+    for (uint64_t i = r0 + blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < r1; i += (uint64_t)gridDim.x * blockDim.x) {
+        Fr sa = Fr::zero(), sb = Fr::zero();
+        for (uint32_t k = A.row_ptr[i]; k < A.row_ptr[i + 1]; ++k) sa = sa + fr_load(A.val + k) * fr_load(z + A.col[k]);
+        for (uint32_t k = B.row_ptr[i]; k < B.row_ptr[i + 1]; ++k) sb = sb + fr_load(B.val + k) * fr_load(z + B.col[k]);
+        fr_store(z + out0 + i, sa * sb);
+    }
+}
+
+// --------------------------------------------------------------- Groth16 setup kernels
+// lag[i] = pref * w^i / (tau - w^i)     (Lagrange basis of the domain at tau)
+__global__ void __launch_bounds__(128) lagrange_kernel(Fr* lag, Fr tau, Fr pref, Fr w, uint64_t m) {
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < m; i += (uint64_t)gridDim.x * blockDim.x) {
+        Fr wi = Fr::one(), b = w;
+        for (uint64_t e = i; e; e >>= 1) { if (e & 1) wi = wi * b; b = b.sqr(); }
+        fr_store(lag + i, pref * wi * (tau - wi).inv());
+    }
+}
+__global__ void csc_hist_kernel(const uint32_t* col, uint64_t nnz, uint32_t* hist) {
+    for (uint64_t k = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; k < nnz; k += (uint64_t)gridDim.x * blockDim.x) atomicAdd(hist + col[k], 1u);
+}
+// entries grouped by column: slot order inside a column is irrelevant (field addition commutes)
+__global__ void csc_scatter_kernel(const uint32_t* row_ptr, const uint32_t* col, uint64_t n_rows, uint32_t* cursor, uint32_t* ent_row, uint32_t* ent_k) {
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n_rows; i += (uint64_t)gridDim.x * blockDim.x)
+        for (uint32_t k = row_ptr[i]; k < row_ptr[i + 1]; ++k) {
+            uint32_t slot = atomicAdd(cursor + col[k], 1u);
+            ent_row[slot] = (uint32_t)i; ent_k[slot] = k;
+        }
+}
+// out[j] = sum over entries of column j of val * lag[row]   (+ lag[n_cons + j] for j <= n_in when add_inputs)
+__global__ void __launch_bounds__(128) qap_column_kernel(const uint32_t* off, const uint32_t* ent_row, const uint32_t* ent_k, const Fr* val, const Fr* lag,
+                                                         uint64_t n_vars, uint64_t n_cons, uint64_t n_in, int add_inputs, Fr* out) {
+    for (uint64_t j = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; j < n_vars; j += (uint64_t)gridDim.x * blockDim.x) {
+        Fr acc = Fr::zero();
+        for (uint32_t e = off[j]; e < off[j + 1]; ++e) acc = acc + fr_load(val + ent_k[e]) * fr_load(lag + ent_row[e]);
+        if (add_inputs && j <= n_in) acc = acc + fr_load(lag + n_cons + j);
+        fr_store(out + j, acc);
+    }
+}
+// k[j] = (beta u_j + alpha v_j + w_j) * (j <= n_in ? gamma^-1 : delta^-1), canonical out
+__global__ void __launch_bounds__(128) setup_k_kernel(const Fr* u, const Fr* v, const Fr* w, Fr alpha, Fr beta, Fr ginv, Fr dinv, uint64_t n_vars, uint64_t n_in, uint32_t* out_canon) {
+    for (uint64_t j = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; j < n_vars; j += (uint64_t)gridDim.x * blockDim.x) {
+        Fr k = (beta * fr_load(u + j) + alpha * fr_load(v + j) + fr_load(w + j)) * (j <= n_in ? ginv : dinv);
+        Fr c; k.to_canonical(c.v);
+        fr_store(reinterpret_cast<Fr*>(out_canon) + j, c);
+    }
+}
+// h scalars: tau^i * zt_over_delta, canonical
+__global__ void __launch_bounds__(128) setup_h_kernel(Fr tau, Fr zd, uint64_t count, uint32_t* out_canon) {
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < count; i += (uint64_t)gridDim.x * blockDim.x) {
+        Fr t = zd, b = tau;
+        for (uint64_t e = i; e; e >>= 1) { if (e & 1) t = t * b; b = b.sqr(); }
+        Fr c; t.to_canonical(c.v);
+        fr_store(reinterpret_cast<Fr*>(out_canon) + i, c);
+    }
+}
+
+// ------------------------------------------------------------------------- host algebra
+static Fr host_fr_from_bytes(const uint8_t* b32, bool* ok) {
+    uint32_t c[8]; memcpy(c, b32, 32);
+    if (Fr::geq_p(c)) { *ok = false; return Fr::zero(); }
+    return Fr::from_canonical(c);
+}
+template <class F> static Xyzz<F> host_scalar_mul(const Xyzz<F>& p, const Fr& k_mont) {
+    uint32_t k[8]; k_mont.to_canonical(k);
+    Xyzz<F> table[16];                                  // 4-bit fixed window
+    table[0] = Xyzz<F>::identity();
+    for (int i = 1; i < 16; ++i) { table[i] = table[i - 1]; table[i].add(p); }
+    Xyzz<F> acc = Xyzz<F>::identity();
+    for (int nib = 63; nib >= 0; --nib) {
+        for (int d = 0; d < 4; ++d) acc = acc.dbl();
+        uint32_t v = (k[nib >> 3] >> (4 * (nib & 7))) & 15u;
+        if (v) acc.add(table[v]);
+    }
+    return acc;
+}
+static Fq host_fq_from_bytes(const uint8_t* b48) { uint32_t c[12]; memcpy(c, b48, 48); return Fq::from_canonical(c); }
+static void host_fq_to_bytes(const Fq& f, uint8_t* b48) { uint32_t c[12]; f.to_canonical(c); memcpy(b48, c, 48); }
+static G1Affine host_g1_from_bytes(const uint8_t* b) { return {host_fq_from_bytes(b), host_fq_from_bytes(b + 48)}; }
+static G2Affine host_g2_from_bytes(const uint8_t* b) {
+    return {{host_fq_from_bytes(b), host_fq_from_bytes(b + 48)}, {host_fq_from_bytes(b + 96), host_fq_from_bytes(b + 144)}};
+}
+static void host_g1_to_bytes(const G1Affine& p, uint8_t* b) { host_fq_to_bytes(p.x, b); host_fq_to_bytes(p.y, b + 48); }
+static void host_g2_to_bytes(const G2Affine& p, uint8_t* b) {
+    host_fq_to_bytes(p.x.c0, b); host_fq_to_bytes(p.x.c1, b + 48); host_fq_to_bytes(p.y.c0, b + 96); host_fq_to_bytes(p.y.c1, b + 144);
+}
+// zcash-style compressed encoding: big-endian x, bit7 compressed,
+// bit6 infinity, bit5 set iff y is the lexicographically larger root.
+static void put_be48(const Fq& x, uint8_t* o) { uint8_t le[48]; host_fq_to_bytes(x, le); for (int i = 0; i < 48; ++i) o[i] = le[47 - i]; }
+static bool fq_larger_half(const Fq& y) {
+    uint32_t a[12], b[12]; y.to_canonical(a); y.neg().to_canonical(b);
+    for (int i = 11; i >= 0; --i) if (a[i] != b[i]) return a[i] > b[i];
+    return false;
+}
+static void compress_g1(const G1Affine& p, uint8_t* o) {
+    if (p.is_identity()) { memset(o, 0, 48); o[0] = 0xC0; return; }
+    put_be48(p.x, o); o[0] |= 0x80; if (fq_larger_half(p.y)) o[0] |= 0x20;
+}
+static void compress_g2(const G2Affine& p, uint8_t* o) {
+    if (p.is_identity()) { memset(o, 0, 96); o[0] = 0xC0; return; }
+    put_be48(p.x.c1, o); put_be48(p.x.c0, o + 48); o[0] |= 0x80;
+    bool larger = p.y.c1.is_zero() ? fq_larger_half(p.y.c0) : fq_larger_half(p.y.c1);
+    if (larger) o[0] |= 0x20;
+}
+
+// ------------------------------------------------------------------------------ key load
+static void free_csr(DevCsr& m) { cudaFree(m.row_ptr); cudaFree(m.col); cudaFree(m.val); m = DevCsr(); }
+static void free_pk(b2g16_pk* pk) {
+    if (!pk) return;
+    free_csr(pk->A); free_csr(pk->B); free_csr(pk->C);
+    cudaFree(pk->a); cudaFree(pk->b_g1); cudaFree(pk->b_g2); cudaFree(pk->l); cudaFree(pk->h);
+    delete pk;
+}
+static void load_csr(Ctx* c, const b2g16_csr& src, uint64_t n_cols, DevCsr& dst, int* d_bad) {
+    B2_REQUIRE(src.row_ptr && (src.nnz == 0 || (src.col && src.val)), B2G16_E_INVALID_ARG, "constraint matrix pointers");
+    B2_REQUIRE(src.nnz < (1ull << 32), B2G16_E_INVALID_ARG, "constraint matrix: nnz must fit 32 bits");
+    B2_REQUIRE(src.row_ptr[0] == 0 && src.row_ptr[src.n_rows] == src.nnz, B2G16_E_INVALID_ARG, "constraint matrix: row_ptr inconsistent with nnz");
+    for (uint64_t k = 0; k < src.nnz; ++k) B2_REQUIRE(src.col[k] < n_cols, B2G16_E_INVALID_ARG, "constraint matrix: column index out of range");
+    dst.n_rows = src.n_rows; dst.nnz = src.nnz;
+    B2_CUDA(cudaMalloc((void**)&dst.row_ptr, (src.n_rows + 1) * sizeof(uint32_t)));
+    B2_CUDA(cudaMalloc((void**)&dst.col, (src.nnz + 1) * sizeof(uint32_t)));
+    B2_CUDA(cudaMalloc((void**)&dst.val, (src.nnz + 1) * sizeof(Fr)));
+    B2_CUDA(cudaMemcpyAsync(dst.row_ptr, src.row_ptr, (src.n_rows + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+    if (src.nnz) {
+        B2_CUDA(cudaMemcpyAsync(dst.col, src.col, src.nnz * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
+        B2_CUDA(cudaMemcpyAsync(dst.val, src.val, src.nnz * 32, cudaMemcpyHostToDevice, c->stream));
+        fr_from_bytes_dev(c, reinterpret_cast<const uint8_t*>(dst.val), dst.val, src.nnz, d_bad);      // in place
+    }
+}
+static b2g16_pk* new_pk_with_cs(Ctx* c, const b2g16_r1cs_view* cs, int* d_bad) {
+    B2_REQUIRE(cs && cs->log_m <= 30, B2G16_E_INVALID_ARG, "constraint system view");
+    const uint64_t m = 1ull << cs->log_m;
+    B2_REQUIRE(cs->n_cons + cs->n_in + 1 <= m, B2G16_E_INVALID_ARG, "domain too small: need n_cons + n_in + 1 <= 2^log_m");
+    B2_REQUIRE(cs->A.n_rows == cs->n_cons && cs->B.n_rows == cs->n_cons && cs->C.n_rows == cs->n_cons, B2G16_E_INVALID_ARG, "matrix row counts");
+    b2g16_pk* pk = new b2g16_pk();
+    pk->log_m = cs->log_m; pk->m = m; pk->n_cons = cs->n_cons; pk->n_in = cs->n_in; pk->n_aux = cs->n_aux;
+    pk->n_vars = 1 + cs->n_in + cs->n_aux;
+    try {
+        load_csr(c, cs->A, pk->n_vars, pk->A, d_bad);
+        load_csr(c, cs->B, pk->n_vars, pk->B, d_bad);
+        load_csr(c, cs->C, pk->n_vars, pk->C, d_bad);
+    } catch (...) { free_pk(pk); throw; }
+    return pk;
+}
+template <class A> static A* upload_points(Ctx* c, const uint8_t* bytes, size_t n, int* d_bad) {
+    A* d = nullptr;
+    B2_CUDA(cudaMalloc((void**)&d, (n + 1) * sizeof(A)));
+    if (n) {
+        // ABI bytes and Montgomery limbs have the same size: convert in place
+        B2_CUDA(cudaMemcpyAsync(d, bytes, n * sizeof(A), cudaMemcpyHostToDevice, c->stream));
+        if (sizeof(A) == sizeof(G1Affine)) g1_from_bytes_dev(c, (const uint8_t*)d, (G1Affine*)d, n, d_bad, true);
+        else g2_from_bytes_dev(c, (const uint8_t*)d, (G2Affine*)d, n, d_bad, true);
+    }
+    return d;
+}
+
+// ---------------------------------------------------------------------------- the prover
+struct MsmOut { uint8_t a[96], b1[96], l[96], h[96], b2[192]; };
+
+static void prove_one(Ctx* c, const b2g16_pk* pk, const uint8_t* d_z_canon, const uint8_t* r32, const uint8_t* s32,
+                      uint8_t* proof_out, b2g16_trace* tr) {
+    bool ok = true;
+    const Fr r = host_fr_from_bytes(r32, &ok), s = host_fr_from_bytes(s32, &ok);
+    B2_REQUIRE(ok, B2G16_E_NOT_CANONICAL, "r / s not canonical");
+    const uint64_t m = pk->m, nv = pk->n_vars;
+    cudaStream_t st = c->stream;
+    cudaEvent_t ev[5];
+    for (auto& e : ev) B2_CUDA(cudaEventCreate(&e));
+    DevFlag bad(c);
+    DevBuf<Fr> z(nv, st), a(m, st), b(m, st), cc(m, st);
+    DevBuf<uint32_t> h(m * 8, st);
+    DevBuf<uint8_t> d_out(sizeof(MsmOut), st);
+    MsmOut out;
+    B2_CUDA(cudaEventRecord(ev[0], st));
+    fr_from_bytes_dev(c, d_z_canon, z.get(), nv, bad.ptr());
+    B2_CUDA(cudaEventRecord(ev[1], st));
+    abc_spmv_kernel<<<grid_for(m, 256), 256, 0, st>>>(pk->A, pk->B, pk->C, z.get(), pk->n_cons, pk->n_in, m, a.get(), b.get(), cc.get());
+    c->launches++;
+    B2_CUDA(cudaGetLastError());
+    if (tr && (tr->a || tr->b || tr->c)) {
+        DevBuf<uint8_t> tmp(m * 32, st);
+        uint8_t* dst[3] = {tr->a, tr->b, tr->c};
+        Fr* src[3] = {a.get(), b.get(), cc.get()};
+        for (int i = 0; i < 3; ++i) if (dst[i]) {
+            fr_to_bytes_dev(c, src[i], tmp.get(), m);
+            B2_CUDA(cudaMemcpyAsync(dst[i], tmp.get(), m * 32, cudaMemcpyDeviceToHost, st));
+            B2_CUDA(cudaStreamSynchronize(st));
+        }
+    }
+    B2_CUDA(cudaEventRecord(ev[2], st));
+    // witness MSMs do not depend on H: fork them onto the aux streams while the NTT chain runs
+    B2_CUDA(cudaEventRecord(c->ev_fork, st));
+    for (int i = 0; i < 4; ++i) B2_CUDA(cudaStreamWaitEvent(c->aux[i], c->ev_fork, 0));
+    const uint32_t* zc = reinterpret_cast<const uint32_t*>(d_z_canon);
+    uint8_t* o = d_out.get();
+    msm_g2_dev(c, pk->b_g2, zc, nv, o + offsetof(MsmOut, b2), c->aux[0], 0);
+    msm_g1_dev(c, pk->a, zc, nv, o + offsetof(MsmOut, a), c->aux[1], 0);
+    msm_g1_dev(c, pk->b_g1, zc, nv, o + offsetof(MsmOut, b1), c->aux[2], 0);
+    msm_g1_dev(c, pk->l, zc + 8 * (1 + pk->n_in), pk->n_aux, o + offsetof(MsmOut, l), c->aux[3], 0);
+    h_from_abc_dev(c, a.get(), b.get(), cc.get(), (int)pk->log_m, h.get(), false, nullptr);
+    B2_CUDA(cudaEventRecord(ev[3], st));
+    msm_g1_dev(c, pk->h, h.get(), m - 1, o + offsetof(MsmOut, h), st, 0);
+    for (int i = 0; i < 4; ++i) { B2_CUDA(cudaEventRecord(c->ev_join[i], c->aux[i])); B2_CUDA(cudaStreamWaitEvent(st, c->ev_join[i], 0)); }
+    B2_CUDA(cudaMemcpyAsync(&out, o, sizeof(MsmOut), cudaMemcpyDeviceToHost, st));
+    if (tr && tr->h) B2_CUDA(cudaMemcpyAsync(tr->h, h.get(), m * 32, cudaMemcpyDeviceToHost, st));
+    B2_CUDA(cudaEventRecord(ev[4], st));
+    bad.check("assignment");                              // synchronises the stream
+
+    // host assembly
+    G1Xyzz Abar = G1Xyzz::from_affine(host_g1_from_bytes(out.a)), B1bar = G1Xyzz::from_affine(host_g1_from_bytes(out.b1));
+    G1Xyzz Lbar = G1Xyzz::from_affine(host_g1_from_bytes(out.l)), Hbar = G1Xyzz::from_affine(host_g1_from_bytes(out.h));
+    G2Xyzz B2bar = G2Xyzz::from_affine(host_g2_from_bytes(out.b2));
+    G1Xyzz D1 = G1Xyzz::from_affine(pk->delta_g1);
+    G2Xyzz D2 = G2Xyzz::from_affine(pk->delta_g2);
+    G1Xyzz A = Abar; A.add_mixed(pk->alpha_g1); A.add(host_scalar_mul(D1, r));
+    G2Xyzz Bq = B2bar; Bq.add_mixed(pk->beta_g2); Bq.add(host_scalar_mul(D2, s));
+    G1Xyzz B1 = B1bar; B1.add_mixed(pk->beta_g1); B1.add(host_scalar_mul(D1, s));
+    G1Xyzz Cc = Hbar; Cc.add(Lbar); Cc.add(host_scalar_mul(A, s)); Cc.add(host_scalar_mul(B1, r)); Cc.add(host_scalar_mul(D1, r * s).neg());
+    G1Affine Aa = A.to_affine(), Ca = Cc.to_affine();
+    G2Affine Ba = Bq.to_affine();
+    compress_g1(Aa, proof_out); compress_g2(Ba, proof_out + 48); compress_g1(Ca, proof_out + 144);
+    if (tr) {
+        if (tr->msm_a) memcpy(tr->msm_a, out.a, 96);
+        if (tr->msm_b1) memcpy(tr->msm_b1, out.b1, 96);
+        if (tr->msm_l) memcpy(tr->msm_l, out.l, 96);
+        if (tr->msm_h) memcpy(tr->msm_h, out.h, 96);
+        if (tr->msm_b2) memcpy(tr->msm_b2, out.b2, 192);
+        if (tr->A) host_g1_to_bytes(Aa, tr->A);
+        if (tr->B) host_g2_to_bytes(Ba, tr->B);
+        if (tr->C) host_g1_to_bytes(Ca, tr->C);
+        for (int i = 0; i < 8; ++i) tr->stage_ms[i] = 0.f;
+        for (int i = 0; i < 4; ++i) cudaEventElapsedTime(&tr->stage_ms[i], ev[i], ev[i + 1]);   // ingest, abc, ntt/h, msm_h + join of the rest
+    }
+    for (auto& e : ev) cudaEventDestroy(e);
+}
+
+}  // namespace b2
+
+using namespace b2;
+
+extern "C" {
+
+int b2g16_pk_load(b2g16_ctx* hctx, const b2g16_pk_view* v, b2g16_pk** out) {
+    Ctx* c = reinterpret_cast<Ctx*>(hctx);
+    if (!c || !v || !out) return B2G16_E_INVALID_ARG;
+    *out = nullptr;
+    return guard(c, [&] {
+        B2_REQUIRE(v->alpha_g1 && v->beta_g1 && v->delta_g1 && v->beta_g2 && v->delta_g2 && v->a && v->b_g1 && v->b_g2 && v->h && v->cs,
+                   B2G16_E_INVALID_ARG, "proving key view has null members");
+        DevFlag bad(c);
+        b2g16_pk* pk = new_pk_with_cs(c, v->cs, bad.ptr());
+        try {
+            B2_REQUIRE(pk->n_aux == 0 || v->l, B2G16_E_INVALID_ARG, "l query missing");
+            pk->a = upload_points<G1Affine>(c, v->a, pk->n_vars, bad.ptr());
+            pk->b_g1 = upload_points<G1Affine>(c, v->b_g1, pk->n_vars, bad.ptr());
+            pk->b_g2 = upload_points<G2Affine>(c, v->b_g2, pk->n_vars, bad.ptr());
+            pk->l = upload_points<G1Affine>(c, v->l, pk->n_aux, bad.ptr());
+            pk->h = upload_points<G1Affine>(c, v->h, pk->m - 1, bad.ptr());
+            // single elements: validate through the same device path, keep host copies
+            DevBuf<uint8_t> small(96 * 3 + 192 * 2, c->stream);
+            uint8_t hb[96 * 3 + 192 * 2];
+            memcpy(hb, v->alpha_g1, 96); memcpy(hb + 96, v->beta_g1, 96); memcpy(hb + 192, v->delta_g1, 96);
+            memcpy(hb + 288, v->beta_g2, 192); memcpy(hb + 480, v->delta_g2, 192);
+            B2_CUDA(cudaMemcpyAsync(small.get(), hb, sizeof(hb), cudaMemcpyHostToDevice, c->stream));
+            g1_from_bytes_dev(c, small.get(), (G1Affine*)small.get(), 3, bad.ptr(), true);
+            g2_from_bytes_dev(c, small.get() + 288, (G2Affine*)(small.get() + 288), 2, bad.ptr(), true);
+            bad.check("proving key");
+            pk->alpha_g1 = host_g1_from_bytes(v->alpha_g1); pk->beta_g1 = host_g1_from_bytes(v->beta_g1); pk->delta_g1 = host_g1_from_bytes(v->delta_g1);
+            pk->beta_g2 = host_g2_from_bytes(v->beta_g2); pk->delta_g2 = host_g2_from_bytes(v->delta_g2);
+        } catch (...) { cudaStreamSynchronize(c->stream); free_pk(pk); throw; }
+        *out = pk;
+    });
+}
+
+int b2g16_pk_free(b2g16_ctx* hctx, b2g16_pk* pk) {
+    Ctx* c = reinterpret_cast<Ctx*>(hctx);
+    if (!c || !pk) return B2G16_E_INVALID_ARG;
+    return guard(c, [&] { B2_CUDA(cudaStreamSynchronize(c->stream)); free_pk(pk); });
+}
+
+int b2g16_pk_export(b2g16_ctx* hctx, const b2g16_pk* pk, int which, uint8_t* out, size_t out_bytes) {
+    Ctx* c = reinterpret_cast<Ctx*>(hctx);
+    if (!c || !pk || !out || which < 0 || which > 9) return B2G16_E_INVALID_ARG;
+    return guard(c, [&] {
+        if (which >= 5) {
+            const size_t need = which >= 8 ? 192 : 96;
+            B2_REQUIRE(out_bytes >= need, B2G16_E_INVALID_ARG, "output buffer too small");
+            switch (which) {
+                case 5: host_g1_to_bytes(pk->alpha_g1, out); break;
+                case 6: host_g1_to_bytes(pk->beta_g1, out); break;
+                case 7: host_g1_to_bytes(pk->delta_g1, out); break;
+                case 8: host_g2_to_bytes(pk->beta_g2, out); break;
+                default: host_g2_to_bytes(pk->delta_g2, out);
+            }
+            return;
+        }
+        const size_t counts[5] = {pk->n_vars, pk->n_vars, pk->n_vars, pk->n_aux, pk->m - 1};
+        const size_t enc = which == 2 ? 192 : 96, n = counts[which];
+        B2_REQUIRE(out_bytes >= n * enc, B2G16_E_INVALID_ARG, "output buffer too small");
+        if (!n) return;
+        DevBuf<uint8_t> raw(n * enc, c->stream);
+        switch (which) {
+            case 0: g1_to_bytes_dev(c, pk->a, raw.get(), n, c->stream); break;
+            case 1: g1_to_bytes_dev(c, pk->b_g1, raw.get(), n, c->stream); break;
+            case 2: g2_to_bytes_dev(c, pk->b_g2, raw.get(), n, c->stream); break;
+            case 3: g1_to_bytes_dev(c, pk->l, raw.get(), n, c->stream); break;
+            default: g1_to_bytes_dev(c, pk->h, raw.get(), n, c->stream);
+        }
+        B2_CUDA(cudaMemcpyAsync(out, raw.get(), n * enc, cudaMemcpyDeviceToHost, c->stream));
+        B2_CUDA(cudaStreamSynchronize(c->stream));
+    });
+}
+
+int b2g16_prove_device(b2g16_ctx* hctx, const b2g16_pk* pk, const uint8_t* d_assignment32, const uint8_t r32[32], const uint8_t s32[32],
+                       int priority, uint8_t proof_out[192], b2g16_trace* trace) {
+    (void)priority;   // one in-flight proof per context: the guard mutex is the queue (compound_proof.hpp:134 hint)
+    Ctx* c = reinterpret_cast<Ctx*>(hctx);
+    if (!c || !pk || !d_assignment32 || !r32 || !s32 || !proof_out) return B2G16_E_INVALID_ARG;
+    return guard(c, [&] { prove_one(c, pk, d_assignment32, r32, s32, proof_out, trace); });
+}
+
+int b2g16_prove(b2g16_ctx* hctx, const b2g16_pk* pk, const uint8_t* assignment32, const uint8_t r32[32], const uint8_t s32[32],
+                int priority, uint8_t proof_out[192], b2g16_trace* trace) {
+    (void)priority;
+    Ctx* c = reinterpret_cast<Ctx*>(hctx);
+    if (!c || !pk || !assignment32 || !r32 || !s32 || !proof_out) return B2G16_E_INVALID_ARG;
+    return guard(c, [&] {
+        DevBuf<uint8_t> dz(pk->n_vars * 32, c->stream);
+        B2_CUDA(cudaMemcpyAsync(dz.get(), assignment32, pk->n_vars * 32, cudaMemcpyHostToDevice, c->stream));
+        prove_one(c, pk, dz.get(), r32, s32, proof_out, trace);
+    });
+}
+
+int b2g16_prove_batch(b2g16_ctx* hctx, const b2g16_pk* pk, const uint8_t* assignments32, size_t n_partitions,
+                      const uint8_t* r32s, const uint8_t* s32s, int priority, uint8_t* proofs_out) {
+    (void)priority;
+    Ctx* c = reinterpret_cast<Ctx*>(hctx);
+    if (!c || !pk || (n_partitions && (!assignments32 || !r32s || !s32s || !proofs_out))) return B2G16_E_INVALID_ARG;
+    return guard(c, [&] {
+        const size_t zb = pk->n_vars * 32;
+        DevBuf<uint8_t> dz[2] = {DevBuf<uint8_t>(zb, c->stream), DevBuf<uint8_t>(zb, c->stream)};
+        for (size_t k = 0; k < n_partitions; ++k) {
+            B2_CUDA(cudaMemcpyAsync(dz[k & 1].get(), assignments32 + k * zb, zb, cudaMemcpyHostToDevice, c->stream));
+            prove_one(c, pk, dz[k & 1].get(), r32s + 32 * k, s32s + 32 * k, proofs_out + 192 * k, nullptr);
+        }
+    });
+}
+
+int b2g16_synth_witness(b2g16_ctx* hctx, const b2g16_pk* pk, uint8_t* d_assignment32, uint64_t n_free) {
+    Ctx* c = reinterpret_cast<Ctx*>(hctx);
+    if (!c || !pk || !d_assignment32) return B2G16_E_INVALID_ARG;
+    return guard(c, [&] {
+        const uint64_t base = 1 + pk->n_in + n_free;
+        B2_REQUIRE(base + pk->n_cons == pk->n_vars, B2G16_E_INVALID_ARG, "synthetic layout: n_aux must equal n_free + n_cons");
+        DevFlag bad(c);
+        DevBuf<Fr> z(pk->n_vars, c->stream);
+        B2_CUDA(cudaMemsetAsync(z.get(), 0, pk->n_vars * sizeof(Fr), c->stream));
+        fr_from_bytes_dev(c, d_assignment32, z.get(), base, bad.ptr());
+        uint64_t row = 0;
+        while (row < pk->n_cons) {                       // same layering as python/b2g16/synth.py layers()
+            uint64_t visible = base + row;
+            uint64_t size = visible / 2 > 1 ? visible / 2 : 1;
+            if (size > pk->n_cons - row) size = pk->n_cons - row;
+            synth_layer_kernel<<<grid_for(size, 256), 256, 0, c->stream>>>(pk->A, pk->B, z.get(), row, row + size, base);
+            c->launches++;
+            row += size;
+        }
+        B2_CUDA(cudaGetLastError());
+        fr_to_bytes_dev(c, z.get(), d_assignment32, pk->n_vars);
+        bad.check("assignment head");
+    });
+}
+
+int b2g16_pk_generate(b2g16_ctx* hctx, const b2g16_r1cs_view* cs, const uint8_t toxic[160], b2g16_pk** out, uint8_t* vk_out) {
+    Ctx* c = reinterpret_cast<Ctx*>(hctx);
+    if (!c || !cs || !toxic || !out) return B2G16_E_INVALID_ARG;
+    *out = nullptr;
+    return guard(c, [&] {
+        bool ok = true;
+        Fr tx[5];
+        for (int i = 0; i < 5; ++i) tx[i] = host_fr_from_bytes(toxic + 32 * i, &ok);
+        B2_REQUIRE(ok, B2G16_E_NOT_CANONICAL, "toxic waste not canonical");
+        const Fr tau = tx[0], alpha = tx[1], beta = tx[2], gamma = tx[3], delta = tx[4];
+        B2_REQUIRE(!gamma.is_zero() && !delta.is_zero(), B2G16_E_INVALID_ARG, "gamma and delta must be non-zero");
+        cudaStream_t st = c->stream;
+        DevFlag bad(c);
+        b2g16_pk* pk = new_pk_with_cs(c, cs, bad.ptr());
+        try {
+            const uint64_t m = pk->m, nv = pk->n_vars;
+            // Lagrange basis at tau
+            Fr w = host_root_of_unity((int)pk->log_m);
+            Fr tm = tau; for (uint32_t i = 0; i < pk->log_m; ++i) tm = tm.sqr();
+            const Fr zt = tm - Fr::one();
+            uint32_t mc[8] = {(uint32_t)m, (uint32_t)(m >> 32), 0, 0, 0, 0, 0, 0};
+            const Fr pref = zt * Fr::from_canonical(mc).inv();
+            DevBuf<Fr> lag(m, st), u(nv, st), v(nv, st), ww(nv, st);
+            lagrange_kernel<<<grid_for(m, 128), 128, 0, st>>>(lag.get(), tau, pref, w, m); c->launches++;
+            // u, v, w = A^T lag, B^T lag, C^T lag via a column grouping (counting sort by column)
+            const DevCsr* mats[3] = {&pk->A, &pk->B, &pk->C};
+            Fr* outs[3] = {u.get(), v.get(), ww.get()};
+            const int n_tiles = (int)((nv + SCAN_TILE - 1) / SCAN_TILE);
+            for (int t = 0; t < 3; ++t) {
+                const DevCsr& M = *mats[t];
+                DevBuf<uint32_t> hist(nv + 1, st), off(nv + 1, st), cursor(nv + 1, st), tile_sums((size_t)n_tiles + 1, st), ent_row(M.nnz + 1, st), ent_k(M.nnz + 1, st);
+                B2_CUDA(cudaMemsetAsync(hist.get(), 0, (nv + 1) * sizeof(uint32_t), st));
+                if (M.nnz) { csc_hist_kernel<<<grid_for(M.nnz, 256), 256, 0, st>>>(M.col, M.nnz, hist.get()); c->launches++; }
+                scan_u32(c, st, hist.get(), off.get(), nv, 0, 1, tile_sums.get());
+                B2_CUDA(cudaMemcpyAsync(cursor.get(), off.get(), (nv + 1) * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+                if (M.nnz) { csc_scatter_kernel<<<grid_for(M.n_rows, 256), 256, 0, st>>>(M.row_ptr, M.col, M.n_rows, cursor.get(), ent_row.get(), ent_k.get()); c->launches++; }
+                qap_column_kernel<<<grid_for(nv, 128), 128, 0, st>>>(off.get(), ent_row.get(), ent_k.get(), M.val, lag.get(), nv, pk->n_cons, pk->n_in, t == 0, outs[t]); c->launches++;
+                B2_CUDA(cudaGetLastError());
+            }
+            // scalars of every query (canonical), then fixed-base multiplications
+            DevBuf<uint32_t> su(nv * 8, st), sv(nv * 8, st), sk(nv * 8, st), sh((m ? m : 1) * 8, st);
+            fr_to_bytes_dev(c, u.get(), (uint8_t*)su.get(), nv);
+            fr_to_bytes_dev(c, v.get(), (uint8_t*)sv.get(), nv);
+            const Fr ginv = gamma.inv(), dinv = delta.inv();
+            setup_k_kernel<<<grid_for(nv, 128), 128, 0, st>>>(u.get(), v.get(), ww.get(), alpha, beta, ginv, dinv, nv, pk->n_in, sk.get()); c->launches++;
+            if (m > 1) { setup_h_kernel<<<grid_for(m - 1, 128), 128, 0, st>>>(tau, zt * dinv, m - 1, sh.get()); c->launches++; }
+            B2_CUDA(cudaGetLastError());
+            B2_CUDA(cudaMalloc((void**)&pk->a, (nv + 1) * sizeof(G1Affine)));
+            B2_CUDA(cudaMalloc((void**)&pk->b_g1, (nv + 1) * sizeof(G1Affine)));
+            B2_CUDA(cudaMalloc((void**)&pk->b_g2, (nv + 1) * sizeof(G2Affine)));
+            B2_CUDA(cudaMalloc((void**)&pk->l, (pk->n_aux + 1) * sizeof(G1Affine)));
+            B2_CUDA(cudaMalloc((void**)&pk->h, m * sizeof(G1Affine)));
+            gen_mul_g1_dev(c, su.get(), nv, pk->a);
+            gen_mul_g1_dev(c, sv.get(), nv, pk->b_g1);
+            gen_mul_g2_dev(c, sv.get(), nv, pk->b_g2);
+            gen_mul_g1_dev(c, sk.get() + 8 * (1 + pk->n_in), pk->n_aux, pk->l);
+            gen_mul_g1_dev(c, sh.get(), m - 1, pk->h);
+            // single elements and the verifying key: alpha, beta, delta in G1; beta, gamma, delta in G2; IC
+            const size_t n_ic = pk->n_in + 1;
+            DevBuf<uint32_t> s1(8 * 8, st);
+            uint32_t hs[6][8];
+            alpha.to_canonical(hs[0]); beta.to_canonical(hs[1]); delta.to_canonical(hs[2]); gamma.to_canonical(hs[3]);
+            B2_CUDA(cudaMemcpyAsync(s1.get(), hs, sizeof(uint32_t) * 32, cudaMemcpyHostToDevice, st));
+            DevBuf<G1Affine> e1(3, st), ic(n_ic, st);
+            DevBuf<G2Affine> e2(3, st);
+            gen_mul_g1_dev(c, s1.get(), 3, e1.get());                 // alpha, beta, delta
+            gen_mul_g2_dev(c, s1.get() + 8, 3, e2.get());             // beta, delta, gamma
+            gen_mul_g1_dev(c, sk.get(), n_ic, ic.get());
+            G1Affine h1[3]; G2Affine h2[3];
+            B2_CUDA(cudaMemcpyAsync(h1, e1.get(), sizeof(h1), cudaMemcpyDeviceToHost, st));
+            B2_CUDA(cudaMemcpyAsync(h2, e2.get(), sizeof(h2), cudaMemcpyDeviceToHost, st));
+            std::vector<uint8_t> icb(96 * n_ic);
+            if (vk_out) {
+                DevBuf<uint8_t> raw(96 * n_ic, st);
+                g1_to_bytes_dev(c, ic.get(), raw.get(), n_ic, st);
+                B2_CUDA(cudaMemcpyAsync(icb.data(), raw.get(), 96 * n_ic, cudaMemcpyDeviceToHost, st));
+                B2_CUDA(cudaStreamSynchronize(st));
+            }
+            bad.check("constraint system");
+            pk->alpha_g1 = h1[0]; pk->beta_g1 = h1[1]; pk->delta_g1 = h1[2];
+            pk->beta_g2 = h2[0]; pk->delta_g2 = h2[1];
+            if (vk_out) {
+                host_g1_to_bytes(h1[0], vk_out); host_g2_to_bytes(h2[0], vk_out + 96);
+                host_g2_to_bytes(h2[2], vk_out + 288); host_g2_to_bytes(h2[1], vk_out + 480);
+                memcpy(vk_out + 672, icb.data(), 96 * n_ic);
+            }
+        } catch (...) { cudaStreamSynchronize(c->stream); free_pk(pk); throw; }
+        *out = pk;
+    });
+}
+
+}  // extern "C"

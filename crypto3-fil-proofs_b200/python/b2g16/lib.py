@@ -1,0 +1,300 @@
+"""ctypes binding of lib/libb2g16.so (the C ABI of include/b2g16.h).
+
+This is the product path: every call goes to the CUDA library.  There is no CPU
+fallback -- if the shared library is missing or no CUDA device is present the import /
+Context() raises.  Host arrays are numpy uint8 in the ABI encodings (see codec.py);
+device buffers are passed as raw pointers (e.g. torch uint8 CUDA tensors' data_ptr()).
+"""
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+PKG_ROOT = os.path.dirname(os.path.dirname(_HERE))
+SO_PATH = os.path.join(PKG_ROOT, "lib", "libb2g16.so")
+
+ERRORS = {-1: "INVALID_ARG", -2: "NOT_CANONICAL", -3: "NOT_ON_CURVE", -4: "CUDA", -5: "NCCL", -6: "OOM", -7: "INTERNAL"}
+
+
+class B2g16Error(RuntimeError):
+    def __init__(self, code, msg):
+        super().__init__("b2g16 error %s (%d): %s" % (ERRORS.get(code, "?"), code, msg))
+        self.code = code
+
+
+class Csr(C.Structure):
+    _fields_ = [("n_rows", C.c_uint64), ("nnz", C.c_uint64), ("row_ptr", C.c_void_p), ("col", C.c_void_p), ("val", C.c_void_p)]
+
+
+class R1csView(C.Structure):
+    _fields_ = [("log_m", C.c_uint32), ("n_cons", C.c_uint64), ("n_in", C.c_uint64), ("n_aux", C.c_uint64),
+                ("A", Csr), ("B", Csr), ("C", Csr)]
+
+
+class PkView(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("alpha_g1", "beta_g1", "delta_g1", "beta_g2", "delta_g2", "a", "b_g1", "b_g2", "l", "h")] + \
+               [("cs", C.POINTER(R1csView))]
+
+
+class Trace(C.Structure):
+    _fields_ = [(n, C.c_void_p) for n in ("a", "b", "c", "h", "msm_a", "msm_b1", "msm_l", "msm_h", "msm_b2", "A", "C", "B")] + \
+               [("stage_ms", C.c_float * 8)]
+
+
+_lib = None
+
+
+def load():
+    """dlopen the CUDA library (raises OSError if it has not been built)."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(SO_PATH):
+            raise OSError("libb2g16.so not built: run `make -C %s` (or __graft_entry__.build())" % PKG_ROOT)
+        _lib = C.CDLL(SO_PATH)
+        _lib.b2g16_last_error.restype = C.c_char_p
+        _lib.b2g16_launch_count.restype = C.c_uint64
+        _lib.b2g16_bases_count.restype = C.c_size_t
+    return _lib
+
+
+def _p(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+def _u8(a, width=None):
+    a = np.ascontiguousarray(a, dtype=np.uint8)
+    if width is not None:
+        a = a.reshape(-1, width)
+    return a
+
+
+class Bases:
+    """Device-resident affine points (proving-key query or synthetic set)."""
+
+    def __init__(self, ctx, handle, group):
+        self.ctx, self.h, self.group = ctx, handle, group
+
+    def __len__(self):
+        return load().b2g16_bases_count(self.h)
+
+    def download(self, first=0, count=None):
+        count = len(self) - first if count is None else count
+        out = np.zeros((count, 96 if self.group == 1 else 192), dtype=np.uint8)
+        self.ctx._chk(load().b2g16_bases_download(self.ctx.h, self.h, C.c_size_t(first), C.c_size_t(count), _p(out)))
+        return out
+
+    def free(self):
+        if self.h:
+            load().b2g16_bases_free(self.ctx.h, self.h)
+            self.h = None
+
+
+class ProvingKey:
+    def __init__(self, ctx, handle, keepalive=None):
+        self.ctx, self.h, self._keep = ctx, handle, keepalive
+
+    def export(self, which, count):
+        sizes = {0: 96, 1: 96, 2: 192, 3: 96, 4: 96, 5: 96, 6: 96, 7: 96, 8: 192, 9: 192}
+        out = np.zeros((count, sizes[which]), dtype=np.uint8)
+        self.ctx._chk(load().b2g16_pk_export(self.ctx.h, self.h, which, _p(out), C.c_size_t(out.nbytes)))
+        return out
+
+    def free(self):
+        if self.h:
+            load().b2g16_pk_free(self.ctx.h, self.h)
+            self.h = None
+
+
+class Context:
+    def __init__(self, device=0, stream=None):
+        self.h = C.c_void_p()
+        rc = load().b2g16_init(int(device), C.c_void_p(stream) if stream else None, C.byref(self.h))
+        if rc != 0:
+            raise B2g16Error(rc, "b2g16_init failed (no CUDA device / bad ordinal)")
+
+    def close(self):
+        if self.h:
+            load().b2g16_shutdown(self.h)
+            self.h = None
+
+    def _chk(self, rc):
+        if rc != 0:
+            raise B2g16Error(rc, load().b2g16_last_error(self.h).decode())
+
+    def synchronize(self):
+        self._chk(load().b2g16_synchronize(self.h))
+
+    @property
+    def launches(self):
+        return int(load().b2g16_launch_count(self.h))
+
+    # ---- multiexp
+    def msm_g1(self, bases, scalars):
+        bases, scalars = _u8(bases, 96), _u8(scalars, 32)
+        out = np.zeros(96, dtype=np.uint8)
+        self._chk(load().b2g16_msm_g1(self.h, _p(bases), _p(scalars), C.c_size_t(scalars.shape[0]), _p(out)))
+        return out
+
+    def msm_g2(self, bases, scalars):
+        bases, scalars = _u8(bases, 192), _u8(scalars, 32)
+        out = np.zeros(192, dtype=np.uint8)
+        self._chk(load().b2g16_msm_g2(self.h, _p(bases), _p(scalars), C.c_size_t(scalars.shape[0]), _p(out)))
+        return out
+
+    def bases_upload(self, group, pts):
+        pts = _u8(pts, 96 if group == 1 else 192)
+        h = C.c_void_p()
+        fn = load().b2g16_bases_upload_g1 if group == 1 else load().b2g16_bases_upload_g2
+        self._chk(fn(self.h, _p(pts), C.c_size_t(pts.shape[0]), C.byref(h)))
+        return Bases(self, h, group)
+
+    def bases_generate(self, group, d_scalars_ptr, n):
+        h = C.c_void_p()
+        self._chk(load().b2g16_bases_generate(self.h, int(group), C.c_void_p(d_scalars_ptr), C.c_size_t(n), C.byref(h)))
+        return Bases(self, h, group)
+
+    def msm_resident(self, bases, d_scalars_ptr, n, first=0):
+        out = np.zeros(96 if bases.group == 1 else 192, dtype=np.uint8)
+        self._chk(load().b2g16_msm_resident(self.h, bases.h, C.c_size_t(first), C.c_void_p(d_scalars_ptr), C.c_size_t(n), _p(out)))
+        return out
+
+    def msm_resident_async(self, bases, d_scalars_ptr, n, d_out_ptr, first=0):
+        self._chk(load().b2g16_msm_resident_async(self.h, bases.h, C.c_size_t(first), C.c_void_p(d_scalars_ptr), C.c_size_t(n), C.c_void_p(d_out_ptr)))
+
+    def g1_sum(self, pts):
+        pts = _u8(pts, 96)
+        out = np.zeros(96, dtype=np.uint8)
+        self._chk(load().b2g16_g1_sum(self.h, _p(pts), C.c_size_t(pts.shape[0]), _p(out)))
+        return out
+
+    def g2_sum(self, pts):
+        pts = _u8(pts, 192)
+        out = np.zeros(192, dtype=np.uint8)
+        self._chk(load().b2g16_g2_sum(self.h, _p(pts), C.c_size_t(pts.shape[0]), _p(out)))
+        return out
+
+    # ---- evaluation domain
+    def ntt(self, data, inverse=False, coset=False):
+        d = _u8(data, 32).copy()
+        n = d.shape[0]
+        log_n = n.bit_length() - 1
+        if n == 0 or (1 << log_n) != n:
+            raise B2g16Error(-1, "domain size must be a power of two")
+        self._chk(load().b2g16_ntt(self.h, _p(d), C.c_uint(log_n), int(inverse), int(coset)))
+        return d
+
+    def ntt_device(self, d_ptr, log_n, inverse=False, coset=False):
+        self._chk(load().b2g16_ntt_device(self.h, C.c_void_p(d_ptr), C.c_uint(log_n), int(inverse), int(coset)))
+
+    def h_from_abc(self, a, b, c):
+        a, b, c = _u8(a, 32), _u8(b, 32), _u8(c, 32)
+        m = a.shape[0]
+        log_m = m.bit_length() - 1
+        if m == 0 or (1 << log_m) != m or b.shape[0] != m or c.shape[0] != m:
+            raise B2g16Error(-1, "a, b, c must have the same power-of-two length")
+        out = np.zeros((m, 32), dtype=np.uint8)
+        self._chk(load().b2g16_h_from_abc(self.h, _p(a), _p(b), _p(c), C.c_uint(log_m), _p(out)))
+        return out
+
+    # ---- parity / measurement aids
+    def field_op(self, field, op, a, b=None):
+        code = {"add": 0, "sub": 1, "mul": 2, "inv": 3, "sqr": 4, "neg": 5}[op]
+        a = _u8(a, 32 if field == "fr" else 48)
+        b = a if b is None else _u8(b, a.shape[1])
+        out = np.empty_like(a)
+        self._chk(load().b2g16_field_op(self.h, 0 if field == "fr" else 1, code, _p(a), _p(b), C.c_size_t(a.shape[0]), _p(out)))
+        return out
+
+    def mad32_peak(self):
+        v, ms = C.c_double(), C.c_double()
+        self._chk(load().b2g16_measure_mad32_peak(self.h, C.byref(v), C.byref(ms)))
+        return v.value, ms.value
+
+    def set_msm_timing(self, on):
+        self._chk(load().b2g16_set_msm_timing(self.h, int(on)))
+
+    def set_msm_window(self, c):
+        self._chk(load().b2g16_set_msm_window(self.h, int(c)))
+
+    def last_msm_timing(self):
+        out = (C.c_float * 5)()
+        self._chk(load().b2g16_last_msm_timing(self.h, out))
+        return dict(zip(("digits_hist", "scan", "scatter", "accumulate", "reduce"), [float(x) for x in out]))
+
+    # ---- prover
+    def pk_load(self, key, cs):
+        """key: object with numpy fields alpha_g1.. h (ABI encodings); cs: object with
+        log_m, n_in, n_aux, n_cons and mats = [(row_ptr, col, val)] * 3."""
+        view, keep = _pk_view(key, cs)
+        h = C.c_void_p()
+        self._chk(load().b2g16_pk_load(self.h, C.byref(view), C.byref(h)))
+        return ProvingKey(self, h, keep)
+
+    def pk_generate(self, cs, toxic, want_vk=False):
+        r1, keep = _r1cs_view(cs)
+        h = C.c_void_p()
+        vk = np.zeros(96 + 3 * 192 + 96 * (cs.n_in + 1), dtype=np.uint8) if want_vk else None
+        self._chk(load().b2g16_pk_generate(self.h, C.byref(r1), _p(_u8(toxic)), C.byref(h), _p(vk)))
+        pk = ProvingKey(self, h, keep)
+        return (pk, vk) if want_vk else pk
+
+    def prove(self, pk, assignment, r, s, priority=False, trace_m=None):
+        z = _u8(assignment, 32)
+        proof = np.zeros(192, dtype=np.uint8)
+        tr, bufs = None, {}
+        if trace_m is not None:
+            tr = Trace()
+            sizes = dict(a=(trace_m, 32), b=(trace_m, 32), c=(trace_m, 32), h=(trace_m, 32), msm_a=(96,), msm_b1=(96,), msm_l=(96,),
+                         msm_h=(96,), msm_b2=(192,), A=(96,), C=(96,), B=(192,))
+            for n, shp in sizes.items():
+                bufs[n] = np.zeros(shp, dtype=np.uint8)
+                setattr(tr, n, _p(bufs[n]))
+        self._chk(load().b2g16_prove(self.h, pk.h, _p(z), _p(_u8(r)), _p(_u8(s)), int(priority), _p(proof), C.byref(tr) if tr else None))
+        if tr is not None:
+            bufs["stage_ms"] = [float(x) for x in tr.stage_ms]
+            return proof.tobytes(), bufs
+        return proof.tobytes()
+
+    def prove_device(self, pk, d_assignment_ptr, r, s, priority=False):
+        proof = np.zeros(192, dtype=np.uint8)
+        self._chk(load().b2g16_prove_device(self.h, pk.h, C.c_void_p(d_assignment_ptr), _p(_u8(r)), _p(_u8(s)), int(priority), _p(proof), None))
+        return proof.tobytes()
+
+    def prove_batch(self, pk, assignments, rs, ss, priority=False):
+        z = _u8(assignments)
+        n = _u8(rs, 32).shape[0]
+        proofs = np.zeros(192 * n, dtype=np.uint8)
+        self._chk(load().b2g16_prove_batch(self.h, pk.h, _p(z), C.c_size_t(n), _p(_u8(rs)), _p(_u8(ss)), int(priority), _p(proofs)))
+        return proofs.tobytes()
+
+    def synth_witness(self, pk, d_assignment_ptr, n_free):
+        self._chk(load().b2g16_synth_witness(self.h, pk.h, C.c_void_p(d_assignment_ptr), C.c_uint64(n_free)))
+
+
+def _r1cs_view(cs):
+    keep = []
+    v = R1csView()
+    v.log_m, v.n_cons, v.n_in, v.n_aux = cs.log_m, cs.n_cons, cs.n_in, cs.n_aux
+    for name, (rp, col, val) in zip("ABC", cs.mats):
+        rp = np.ascontiguousarray(rp, dtype=np.uint32)
+        col = np.ascontiguousarray(col, dtype=np.uint32)
+        val = _u8(val, 32)
+        keep += [rp, col, val]
+        m = Csr()
+        m.n_rows, m.nnz = cs.n_cons, col.shape[0]
+        m.row_ptr, m.col, m.val = _p(rp), _p(col), _p(val)
+        setattr(v, name, m)
+    return v, keep
+
+
+def _pk_view(key, cs):
+    r1, keep = _r1cs_view(cs)
+    keep.append(r1)
+    v = PkView()
+    for n in ("alpha_g1", "beta_g1", "delta_g1", "beta_g2", "delta_g2", "a", "b_g1", "b_g2", "l", "h"):
+        arr = _u8(getattr(key, n))
+        keep.append(arr)
+        setattr(v, n, _p(arr))
+    v.cs = C.pointer(r1)
+    return v, keep

@@ -1,0 +1,348 @@
+"""GPU parity: the CUDA path (through the C ABI of include/b2g16.h) against the CPU oracle
+and the committed golden vectors.  Bit-exact everywhere -- all arithmetic is integer.
+Mirrors the reference's test tiers: field/encoding KATs
+(libs/storage/test/core/fr32.cpp:51-85), then transform / multiexp units, then the
+compound `prove` round trip (libs/storage/test/**/compound.cpp)."""
+import numpy as np
+import pytest
+
+from b2g16 import codec, synth
+import util
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def ctx():
+    from b2g16 import lib
+    c = lib.Context(0)
+    yield c
+    c.close()
+
+
+def test_native_library_is_what_runs(ctx):
+    from b2g16 import lib
+    assert lib.SO_PATH.endswith("crypto3-fil-proofs_b200/lib/libb2g16.so")
+    before = ctx.launches
+    rng = np.random.Generator(np.random.PCG64(1))
+    ctx.ntt(codec.random_fr(64, rng))
+    assert ctx.launches > before
+
+
+# ------------------------------------------------------------------------------ fields
+def test_field_ops_golden(ctx):
+    g = util.golden("fields")
+    for f in ("fr", "fq"):
+        a, b = g[f + "_a"], g[f + "_b"]
+        for op in ("add", "sub", "mul", "inv", "sqr", "neg"):
+            got = ctx.field_op(f, op, a, b)
+            assert np.array_equal(got, g[f"{f}_{op}"]), (f, op)
+
+
+@pytest.mark.parametrize("field,width", [("fr", 32), ("fq", 48)])
+def test_field_ops_random(ctx, oracle, field, width):
+    rng = np.random.Generator(np.random.PCG64(7))
+    n = 20000
+    if field == "fr":
+        a, b = codec.random_fr(n, rng), codec.random_fr(n, rng)
+    else:
+        p = 0x1a0111ea397fe69a4b1ba7b6434bacd764774b84f38512bf6730d2a0f6b0f6241eabfffeb153ffffb9feffffffffaaab
+        raw = rng.integers(0, 256, size=(2 * n, 48), dtype=np.uint8)
+        raw[:, 47] &= 0x0F                                   # < 2^380 < p
+        a, b = raw[:n].copy(), raw[n:].copy()
+        a[0] = np.frombuffer((p - 1).to_bytes(48, "little"), dtype=np.uint8)
+        a[1] = 0
+    for op in ("add", "sub", "mul", "sqr", "neg"):
+        assert np.array_equal(ctx.field_op(field, op, a, b), oracle.field_op(field, op, a, b)), op
+    assert np.array_equal(ctx.field_op(field, "inv", a[:512]), oracle.field_op(field, "inv", a[:512]))
+
+
+def test_fr32_canonical_contract(ctx):
+    """libs/storage/test/core/fr32.cpp:51-85 and libs/filecoin/test/api/mod.cpp:35-43:
+    which 32-byte strings are scalars.  The device ingest must reject exactly the same."""
+    from b2g16.lib import B2g16Error
+    cases = [(bytes(range(32)), True), (b"\xff" * 31 + b"\x73", False), (b"\xff" * 31 + b"\x72", True),
+             (b"\xff" * 30 + b"\xec\x73", True), (b"\xff" * 30 + b"\xed\x73", False),
+             (b"\x00" * 32, True), (b"\xff" * 32, False)]
+    for raw, ok in cases:
+        x = np.zeros((4, 32), dtype=np.uint8)
+        x[2] = np.frombuffer(raw, dtype=np.uint8)
+        if ok:
+            back = ctx.ntt(ctx.ntt(x), inverse=True)
+            assert np.array_equal(back, x)
+        else:
+            with pytest.raises(B2g16Error) as e:
+                ctx.ntt(x)
+            assert e.value.code == -2
+
+
+# --------------------------------------------------------------------------------- NTT
+def test_ntt_golden(ctx):
+    g = util.golden("ntt")
+    n_checked = 0
+    for key in g.files:
+        if not key.startswith("in_"):
+            continue
+        ln = int(key.split("_")[1])
+        for inv in (0, 1):
+            for cos in (0, 1):
+                assert np.array_equal(ctx.ntt(g[key], inverse=bool(inv), coset=bool(cos)), g[f"out_{ln}_{inv}{cos}"]), (ln, inv, cos)
+                n_checked += 1
+    assert n_checked >= 8
+
+
+@pytest.mark.parametrize("log_n", [0, 1, 3, 8, 11, 12, 13, 16, 18, 20, 21])
+def test_ntt_vs_oracle(ctx, oracle, log_n):
+    rng = np.random.Generator(np.random.PCG64(100 + log_n))
+    x = codec.random_fr(1 << log_n, rng)
+    modes = [(0, 0), (1, 0), (0, 1), (1, 1)] if log_n <= 16 else [(0, 0), (1, 1)]
+    for inv, cos in modes:
+        assert np.array_equal(ctx.ntt(x, inverse=bool(inv), coset=bool(cos)), oracle.ntt(x, inverse=bool(inv), coset=bool(cos))), (inv, cos)
+
+
+def test_ntt_large_roundtrip_and_point_evaluation(ctx, oracle):
+    """2^24 on device-resident data: inverse(forward(x)) == x, and X[k] = sum x_i w^(ik) checked
+    at a few k through Horner on the CPU for a sparse x (size-independent properties)."""
+    import torch
+    log_n = 24
+    n = 1 << log_n
+    rng = np.random.Generator(np.random.PCG64(5))
+    x = codec.random_fr(n, rng)
+    d = torch.from_numpy(x).cuda()
+    ctx.ntt_device(d.data_ptr(), log_n, inverse=False, coset=False)
+    ctx.synchronize()
+    fwd = d.cpu().numpy()
+    ctx.ntt_device(d.data_ptr(), log_n, inverse=True, coset=False)
+    ctx.synchronize()
+    assert np.array_equal(d.cpu().numpy(), x)
+    # sparse input: X[k] = sum_j x[i_j] w^(i_j k)
+    r = codec.R_MOD
+    w = pow(7, (r - 1) >> log_n, r)
+    idx = [0, 1, 12345, n // 2 + 3, n - 1]
+    sp = np.zeros((n, 32), dtype=np.uint8)
+    vals = codec.fr_to_ints(x[:len(idx)])
+    for i, v in zip(idx, vals):
+        sp[i] = codec.fr_from_ints([v])[0]
+    out = ctx.ntt(sp)
+    for k in (0, 1, 2, 77777, n - 1, n // 2):
+        want = sum(v * pow(w, (i * k) % n, r) for i, v in zip(idx, vals)) % r
+        assert codec.fr_to_ints(out[k:k + 1])[0] == want, k
+    assert fwd.shape == x.shape
+
+
+@pytest.mark.parametrize("log_m", [1, 6, 11, 14, 17])
+def test_h_from_abc_vs_oracle(ctx, oracle, log_m):
+    rng = np.random.Generator(np.random.PCG64(200 + log_m))
+    m = 1 << log_m
+    a, b = codec.random_fr(m, rng), codec.random_fr(m, rng)
+    c = oracle.field_op("fr", "mul", a, b)
+    got = ctx.h_from_abc(a, b, c)
+    assert np.array_equal(got, oracle.h_from_abc(a, b, c))
+    assert not got[m - 1].any()
+
+
+# --------------------------------------------------------------------------------- MSM
+def test_msm_golden(ctx):
+    g = util.golden("msm")
+    ns = sorted(int(k.split("_")[1]) for k in g.files if k.startswith("scalars_"))
+    assert ns
+    for n in ns:
+        assert np.array_equal(ctx.msm_g1(g[f"g1_bases_{n}"], g[f"scalars_{n}"]), g[f"g1_out_{n}"]), n
+        assert np.array_equal(ctx.msm_g2(g[f"g2_bases_{n}"], g[f"scalars_{n}"]), g[f"g2_out_{n}"]), n
+
+
+def _edge_inputs(oracle, n, rng, group):
+    gen = oracle.g1_gen_mul if group == 1 else oracle.g2_gen_mul
+    bases, scal = gen(codec.random_fr(n, rng)), codec.random_fr(n, rng)
+    if n >= 16:
+        scal[0] = 0
+        scal[1] = 0; scal[1, 0] = 1
+        scal[2] = np.frombuffer((codec.R_MOD - 1).to_bytes(32, "little"), dtype=np.uint8)
+        scal[3] = 0; scal[3, 1] = 0x80                    # 2^15: window boundary
+        scal[4] = 0; scal[4, 2] = 1                       # 2^16
+        bases[5] = 0                                      # identity base
+        bases[6] = bases[7]; scal[6] = scal[7]            # equal points in one bucket -> doubling branch
+        bases[8] = bases[9]                               # P and -P in one bucket -> cancellation
+        neg = (codec.R_MOD - codec.fr_to_ints(scal[9:10])[0]) % codec.R_MOD
+        scal[8] = codec.fr_from_ints([neg])[0]
+    return bases, scal
+
+
+@pytest.mark.parametrize("n", [0, 1, 2, 3, 17, 256, 4097, 70000])
+def test_msm_g1_vs_oracle(ctx, oracle, n):
+    rng = np.random.Generator(np.random.PCG64(300 + n))
+    bases, scal = _edge_inputs(oracle, n, rng, 1)
+    assert np.array_equal(ctx.msm_g1(bases, scal), oracle.msm_g1(bases, scal))
+
+
+@pytest.mark.parametrize("n", [0, 1, 17, 300, 5000])
+def test_msm_g2_vs_oracle(ctx, oracle, n):
+    rng = np.random.Generator(np.random.PCG64(400 + n))
+    bases, scal = _edge_inputs(oracle, n, rng, 2)
+    assert np.array_equal(ctx.msm_g2(bases, scal), oracle.msm_g2(bases, scal))
+
+
+@pytest.mark.parametrize("c", [8, 11, 13, 16])
+def test_msm_g1_every_window_size(ctx, oracle, c):
+    rng = np.random.Generator(np.random.PCG64(500 + c))
+    bases, scal = _edge_inputs(oracle, 3000, rng, 1)
+    ctx.set_msm_window(c)
+    try:
+        assert np.array_equal(ctx.msm_g1(bases, scal), oracle.msm_g1(bases, scal))
+    finally:
+        ctx.set_msm_window(0)
+
+
+def test_msm_filecoin_like_skew(ctx, oracle):
+    """Witness-shaped scalars (60 % zero, 20 % one, 10 % < 2^16, 10 % uniform):
+    a few buckets hold most points, which exercises the segment split."""
+    rng = np.random.Generator(np.random.PCG64(9))
+    n = 60000
+    bases = oracle.g1_gen_mul(codec.random_fr(n, rng))
+    scal = codec.random_fr(n, rng)
+    u = rng.random(n)
+    scal[u < 0.6] = 0
+    ones = (u >= 0.6) & (u < 0.8)
+    scal[ones] = 0; scal[ones, 0] = 1
+    small = (u >= 0.8) & (u < 0.9)
+    scal[small, 2:] = 0
+    assert np.array_equal(ctx.msm_g1(bases, scal), oracle.msm_g1(bases, scal))
+
+
+def test_msm_rejects_bad_inputs(ctx, oracle):
+    from b2g16.lib import B2g16Error
+    rng = np.random.Generator(np.random.PCG64(10))
+    bases, scal = oracle.g1_gen_mul(codec.random_fr(8, rng)), codec.random_fr(8, rng)
+    bad_s = scal.copy(); bad_s[3] = 0xFF
+    with pytest.raises(B2g16Error) as e:
+        ctx.msm_g1(bases, bad_s)
+    assert e.value.code == -2
+    bad_b = bases.copy(); bad_b[2, 0] ^= 1                # off the curve
+    with pytest.raises(B2g16Error) as e:
+        ctx.msm_g1(bad_b, scal)
+    assert e.value.code == -3
+
+
+def test_generated_bases_and_resident_range(ctx, oracle):
+    import torch
+    rng = np.random.Generator(np.random.PCG64(11))
+    n = 3000
+    k, s = codec.random_fr(n, rng), codec.random_fr(n, rng)
+    k[0] = 0                                              # 0 * G = identity
+    for group, gen, msm in ((1, oracle.g1_gen_mul, oracle.msm_g1), (2, oracle.g2_gen_mul, oracle.msm_g2)):
+        nn = n if group == 1 else 600
+        dk, ds = torch.from_numpy(k[:nn]).cuda(), torch.from_numpy(s[:nn]).cuda()
+        bases = ctx.bases_generate(group, dk.data_ptr(), nn)
+        want = gen(k[:nn])
+        assert np.array_equal(bases.download(), want)
+        assert np.array_equal(ctx.msm_resident(bases, ds.data_ptr(), nn), msm(want, s[:nn]))
+        first, cnt = 100, 333                             # point-range shard (multi-GPU sharding unit)
+        assert np.array_equal(ctx.msm_resident(bases, ds.data_ptr() + 32 * first, cnt, first=first), msm(want[first:first + cnt], s[first:first + cnt]))
+        bases.free()
+    pts = oracle.g1_gen_mul(k[:5])
+    acc = pts[0]
+    for p in pts[1:]:
+        acc = oracle.g1_add(acc, p)
+    assert np.array_equal(ctx.g1_sum(pts), acc)
+
+
+def test_msm_large_linearity(ctx, oracle):
+    """2^20 points generated on the device: sum_i s_i (k_i G) == (sum_i s_i k_i) G."""
+    import torch
+    n = 1 << 20
+    rng = np.random.Generator(np.random.PCG64(12))
+    k, s = codec.random_fr(n, rng), codec.random_fr(n, rng)
+    dk, ds = torch.from_numpy(k).cuda(), torch.from_numpy(s).cuda()
+    bases = ctx.bases_generate(1, dk.data_ptr(), n)
+    got = ctx.msm_resident(bases, ds.data_ptr(), n)
+    bases.free()
+    ki = np.array(codec.fr_to_ints(k), dtype=object)
+    si = np.array(codec.fr_to_ints(s), dtype=object)
+    tot = int((ki * si).sum() % codec.R_MOD)
+    assert np.array_equal(got, oracle.g1_gen_mul(codec.fr_from_ints([tot]))[0])
+
+
+# ------------------------------------------------------------------------------- prove
+PROOF_FIELDS = (("a", "ev_a"), ("b", "ev_b"), ("c", "ev_c"), ("h", "h_coeffs"), ("msm_a", "msm_a"), ("msm_b1", "msm_b1"),
+                ("msm_b2", "msm_b2"), ("msm_l", "msm_l"), ("msm_h", "msm_h"), ("A", "A"), ("B", "B"), ("C", "C"))
+
+
+class _KeyView:
+    pass
+
+
+@pytest.mark.parametrize("log_m", [4, 7])
+def test_prove_golden(ctx, oracle, log_m):
+    g = util.golden(f"groth16_m{log_m}")
+    s = synth.SynthR1cs(int(g["log_m"]), int(g["n_in"]), int(g["seed"]), n_free=int(g["n_free"]))
+    cs = util.oracle_cs(oracle, s)
+    key = _KeyView()
+    for n in ("alpha_g1", "beta_g1", "delta_g1", "beta_g2", "delta_g2", "a", "b_g1", "b_g2", "l", "h"):
+        setattr(key, n, g[n])
+    pk = ctx.pk_load(key, cs)
+    proof, tr = ctx.prove(pk, g["z"], g["r"], g["s"], trace_m=1 << log_m)
+    for name, gname in PROOF_FIELDS:
+        assert np.array_equal(tr[name], g[gname]), name
+    assert len(proof) == 192 and proof == g["proof"].tobytes()
+    pk.free()
+    # setup on the device from the same toxic waste gives the same key
+    pk2, vk = ctx.pk_generate(cs, g["toxic"], want_vk=True)
+    for which, n in ((0, "a"), (1, "b_g1"), (2, "b_g2"), (3, "l"), (4, "h")):
+        assert np.array_equal(pk2.export(which, g[n].shape[0]), g[n]), n
+    for which, n in ((5, "alpha_g1"), (6, "beta_g1"), (7, "delta_g1"), (8, "beta_g2"), (9, "delta_g2")):
+        assert np.array_equal(pk2.export(which, 1)[0], g[n]), n
+    assert np.array_equal(vk[:96], g["alpha_g1"]) and np.array_equal(vk[96:288], g["beta_g2"])
+    assert np.array_equal(vk[288:480], g["gamma_g2"]) and np.array_equal(vk[480:672], g["delta_g2"])
+    assert np.array_equal(vk[672:].reshape(-1, 96), g["ic"])
+    assert ctx.prove(pk2, g["z"], g["r"], g["s"]) == g["proof"].tobytes()
+    pk2.free()
+
+
+@pytest.mark.parametrize("log_m,n_in", [(10, 3), (13, 39), (16, 1)])
+def test_prove_vs_oracle(ctx, oracle, log_m, n_in):
+    """Random-witness R1CS (BASELINE configs[0] is the 2^16 case): every intermediate and the
+    192 proof bytes equal the CPU prover's for the same key, witness, r and s."""
+    import torch
+    s, cs, z = util.synth_instance(oracle, log_m, n_in, seed=700 + log_m)
+    toxic, r, sr = util.toxic_from_seed(700 + log_m)
+    pk = ctx.pk_generate(cs, toxic)
+    key = oracle.Key(cs)
+    m, nv = 1 << log_m, cs.n_vars
+    for which, n, cnt in ((0, "a", nv), (1, "b_g1", nv), (2, "b_g2", nv), (3, "l", cs.n_aux), (4, "h", m - 1)):
+        setattr(key, n, pk.export(which, cnt))
+    for which, n in ((5, "alpha_g1"), (6, "beta_g1"), (7, "delta_g1"), (8, "beta_g2"), (9, "delta_g2")):
+        setattr(key, n, pk.export(which, 1)[0])
+    if log_m <= 13:                                       # CPU setup is slow beyond this; the prover parity below is what matters
+        okey = oracle.groth16_setup(cs, toxic)
+        for n in ("a", "b_g1", "b_g2", "l", "h", "alpha_g1", "beta_g1", "delta_g1", "beta_g2", "delta_g2"):
+            assert np.array_equal(getattr(key, n), getattr(okey, n)), n
+    want_proof, want = oracle.groth16_prove(key, z, r, sr)
+    proof, tr = ctx.prove(pk, z, r, sr, trace_m=m)
+    for name, _ in PROOF_FIELDS:
+        assert np.array_equal(tr[name], want[name]), name
+    assert proof == want_proof
+    # witness generated on the device equals the oracle's; device-resident proving gives the same bytes
+    dz = torch.zeros((nv, 32), dtype=torch.uint8, device="cuda")
+    dz[: s.z_head.shape[0]] = torch.from_numpy(s.z_head).cuda()
+    ctx.synth_witness(pk, dz.data_ptr(), s.n_free)
+    ctx.synchronize()
+    assert np.array_equal(dz.cpu().numpy(), z)
+    assert ctx.prove_device(pk, dz.data_ptr(), r, sr) == want_proof
+    # multi-partition: concatenation of per-partition proofs (F/api/seal.hpp:304-308)
+    r2 = np.stack([r, sr]); s2 = np.stack([sr, r])
+    both = ctx.prove_batch(pk, np.concatenate([z, z]), r2, s2)
+    assert len(both) == 384 and both[:192] == want_proof
+    assert both[192:] == oracle.groth16_prove(key, z, sr, r, want_trace=False)[0]
+    pk.free()
+
+
+def test_prove_rejects_non_canonical_witness(ctx, oracle):
+    from b2g16.lib import B2g16Error
+    s, cs, z = util.synth_instance(oracle, 6, 2, seed=5)
+    toxic, r, sr = util.toxic_from_seed(5)
+    pk = ctx.pk_generate(cs, toxic)
+    bad = z.copy(); bad[5] = 0xFF
+    with pytest.raises(B2g16Error) as e:
+        ctx.prove(pk, bad, r, sr)
+    assert e.value.code == -2
+    pk.free()
