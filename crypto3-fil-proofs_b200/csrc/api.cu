@@ -33,6 +33,7 @@ int b2g16_init(int device, void* stream, b2g16_ctx** out) {
         uint64_t keep = ~0ull;                                      // keep freed workspace in the pool
         B2_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
         if (const char* e = getenv("B2G16_MSM_C")) c->msm_window_override = atoi(e);
+        if (const char* e = getenv("B2G16_ACC_VARIANT")) c->acc_variant = atoi(e);
         ntt_init_roots(c);
     });
     if (rc != B2G16_OK) { delete c; return rc; }

@@ -117,7 +117,17 @@ template <class F> B2_D Affine<F> load_affine(const Affine<F>* p) {
     for (int i = 0; i < (int)(sizeof(Affine<F>) / 16); ++i) { uint4 t = __ldg(q + i); d[4 * i] = t.x; d[4 * i + 1] = t.y; d[4 * i + 2] = t.z; d[4 * i + 3] = t.w; }
     return r;
 }
-template <class F, int THREADS> __global__ void __launch_bounds__(THREADS)
+template <class F> B2_D Xyzz<F> xyzz_shfl_down(const Xyzz<F>& p, int delta) {
+    Xyzz<F> r;
+    const uint32_t* s = reinterpret_cast<const uint32_t*>(&p);
+    uint32_t* d = reinterpret_cast<uint32_t*>(&r);
+#pragma unroll
+    for (int i = 0; i < (int)(sizeof(Xyzz<F>) / 4); ++i) d[i] = __shfl_down_sync(0xffffffffu, s[i], delta);
+    return r;
+}
+B2_D void prefetch_l2(const void* p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
+template <class F, int THREADS, int MINB, int PF> __global__ void __launch_bounds__(THREADS, MINB)
 msm_accumulate_kernel(const Affine<F>* __restrict__ bases, const uint32_t* __restrict__ sorted, const uint32_t* __restrict__ hist,
                       const uint32_t* __restrict__ off, const uint32_t* __restrict__ seg_off, uint32_t n_buckets, uint32_t S, Xyzz<F>* __restrict__ seg_acc) {
     const uint32_t seg_total = seg_off[n_buckets];
@@ -130,13 +140,59 @@ msm_accumulate_kernel(const Affine<F>* __restrict__ bases, const uint32_t* __res
         const uint32_t bucket_end = off[b] + hist[b];
         const uint32_t end = begin + S < bucket_end ? begin + S : bucket_end;
         Xyzz<F> acc = Xyzz<F>::identity();
-        for (uint32_t e = begin; e < end; ++e) {
-            const uint32_t ix = sorted[e];
+        if (PF == 0) {
+            for (uint32_t e = begin; e < end; ++e) {
+                const uint32_t ix = sorted[e];
+                Affine<F> p = load_affine(bases + (ix & 0x7fffffffu));
+                if (ix >> 31) p.y = p.y.neg();
+                acc.add_mixed(p);
+            }
+        } else if (PF == 1) {
+            // index look-ahead + L2 prefetch of the next point: the 96/192-byte gathers are
+            // random, their DRAM latency otherwise sits on the critical path of every add
+            uint32_t nxt = begin < end ? sorted[begin] : 0u;
+            for (uint32_t e = begin; e < end; ++e) {
+                const uint32_t ix = nxt;
+                if (e + 1 < end) {
+                    nxt = sorted[e + 1];
+                    const char* q = reinterpret_cast<const char*>(bases + (nxt & 0x7fffffffu));
+                    prefetch_l2(q);
+                    prefetch_l2(q + sizeof(Affine<F>) - 4);
+                }
+                Affine<F> p = load_affine(bases + (ix & 0x7fffffffu));
+                if (ix >> 31) p.y = p.y.neg();
+                acc.add_mixed(p);
+            }
+        } else {
+            // register double-buffer: the next point is loaded while the current add runs
+            uint32_t ix = begin < end ? sorted[begin] : 0u;
             Affine<F> p = load_affine(bases + (ix & 0x7fffffffu));
-            if (ix >> 31) p.y = p.y.neg();
-            acc.add_mixed(p);
+            for (uint32_t e = begin; e < end; ++e) {
+                const uint32_t cix = ix;
+                Affine<F> cur = p;
+                if (e + 1 < end) { ix = sorted[e + 1]; p = load_affine(bases + (ix & 0x7fffffffu)); }
+                if (cix >> 31) cur.y = cur.y.neg();
+                acc.add_mixed(cur);
+            }
         }
         seg_acc[seg] = acc;
+    }
+}
+// a bucket that was split into several segments: one warp folds them into its first slot
+template <class F> __global__ void __launch_bounds__(128)
+msm_fold_segments_kernel(Xyzz<F>* __restrict__ seg_acc, const uint32_t* __restrict__ seg_off, uint32_t n_buckets) {
+    const uint32_t lane = threadIdx.x & 31;
+    for (uint32_t b = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; b < n_buckets; b += (gridDim.x * blockDim.x) >> 5) {
+        const uint32_t s0 = seg_off[b], s1 = seg_off[b + 1];
+        if (s1 - s0 <= 1) continue;                      // warp-uniform
+        Xyzz<F> acc = Xyzz<F>::identity();
+        for (uint32_t s = s0 + lane; s < s1; s += 32) { Xyzz<F> t = seg_acc[s]; xyzz_add_call(&acc, &t); }
+        for (int d = 16; d >= 1; d >>= 1) {
+            Xyzz<F> o = xyzz_shfl_down(acc, d);
+            xyzz_add_call(&acc, &o);
+        }
+        __syncwarp();
+        if (lane == 0) seg_acc[s0] = acc;
     }
 }
 
@@ -150,7 +206,7 @@ msm_reduce_kernel(const Xyzz<F>* __restrict__ seg_acc, const uint32_t* __restric
     Xyzz<F> run = Xyzz<F>::identity(), acc = Xyzz<F>::identity();
     for (uint32_t j = lo + per; j-- > lo;) {                    // weights j+1, descending
         const uint32_t b = w * B + j;
-        for (uint32_t s = seg_off[b]; s < seg_off[b + 1]; ++s) { Xyzz<F> t = seg_acc[s]; xyzz_add_call(&run, &t); }
+        if (seg_off[b + 1] > seg_off[b]) { Xyzz<F> t = seg_acc[seg_off[b]]; xyzz_add_call(&run, &t); }
         xyzz_add_call(&acc, &run);
     }
     // acc = sum (j - lo + 1) B_j ;  add lo * run (double-and-add over the bits of lo)
@@ -161,14 +217,6 @@ msm_reduce_kernel(const Xyzz<F>* __restrict__ seg_acc, const uint32_t* __restric
     }
     xyzz_add_call(&acc, &m);
     partial[gid] = acc;
-}
-template <class F> B2_D Xyzz<F> xyzz_shfl_down(const Xyzz<F>& p, int delta) {
-    Xyzz<F> r;
-    const uint32_t* s = reinterpret_cast<const uint32_t*>(&p);
-    uint32_t* d = reinterpret_cast<uint32_t*>(&r);
-#pragma unroll
-    for (int i = 0; i < (int)(sizeof(Xyzz<F>) / 4); ++i) d[i] = __shfl_down_sync(0xffffffffu, s[i], delta);
-    return r;
 }
 // one warp per window: fold the T chunk results
 template <class F> __global__ void __launch_bounds__(32)
@@ -269,6 +317,33 @@ static void scan_u32(Ctx* ctx, cudaStream_t st, const uint32_t* in, uint32_t* ou
     B2_CUDA(cudaGetLastError());
 }
 
+template <class F, int MINB, int PF>
+static void launch_accumulate_v(cudaStream_t st, size_t max_segs, const Affine<F>* bases, const uint32_t* sorted, const uint32_t* hist, const uint32_t* off,
+                                const uint32_t* seg_off, uint32_t nb, uint32_t S, Xyzz<F>* seg_acc) {
+    constexpr int THREADS = sizeof(F) > 48 ? 64 : 128;
+    msm_accumulate_kernel<F, THREADS, MINB, PF><<<grid_for(max_segs, THREADS, 148 * 64), THREADS, 0, st>>>(bases, sorted, hist, off, seg_off, nb, S, seg_acc);
+}
+// variant = 10 * min_blocks_per_SM + prefetch_mode (tuning knob B2G16_ACC_VARIANT; default below)
+template <class F>
+static void launch_accumulate(Ctx* ctx, cudaStream_t st, size_t max_segs, const Affine<F>* bases, const uint32_t* sorted, const uint32_t* hist, const uint32_t* off,
+                              const uint32_t* seg_off, uint32_t nb, uint32_t S, Xyzz<F>* seg_acc) {
+    ctx->launches++;
+#define B2_ACC(MINB, PF) launch_accumulate_v<F, MINB, PF>(st, max_segs, bases, sorted, hist, off, seg_off, nb, S, seg_acc)
+    if (sizeof(F) > 48) { B2_ACC(1, 0); return; }
+    switch (ctx->acc_variant) {
+        case 10: B2_ACC(1, 0); break;
+        case 11: B2_ACC(1, 1); break;
+        case 12: B2_ACC(1, 2); break;
+        case 30: B2_ACC(3, 0); break;
+        case 31: B2_ACC(3, 1); break;
+        case 32: B2_ACC(3, 2); break;
+        case 40: B2_ACC(4, 0); break;
+        case 41: B2_ACC(4, 1); break;
+        default: B2_ACC(1, 0);
+    }
+#undef B2_ACC
+}
+
 template <class F>
 void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size_t n, uint8_t* d_out_bytes, cudaStream_t st, int window_bits) {
     constexpr int OUT_BYTES = (int)sizeof(Affine<F>);
@@ -306,9 +381,8 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
     mark(2);
     msm_scatter_kernel<<<grid_for(n, 256, 148 * 8), 256, 0, st>>>(d_scalars, n, c, W, cursor.get(), sorted.get()); ctx->launches++;
     mark(3);
-    constexpr int ACC_THREADS = sizeof(F) > 48 ? 64 : 128;
-    msm_accumulate_kernel<F, ACC_THREADS><<<grid_for(max_segs, ACC_THREADS, 148 * 64), ACC_THREADS, 0, st>>>(
-        d_bases, sorted.get(), hist.get(), off.get(), seg_off.get(), (uint32_t)nb, S, seg_acc.get()); ctx->launches++;
+    launch_accumulate<F>(ctx, st, max_segs, d_bases, sorted.get(), hist.get(), off.get(), seg_off.get(), (uint32_t)nb, S, seg_acc.get());
+    msm_fold_segments_kernel<F><<<grid_for(nb * 32, 128, 148 * 16), 128, 0, st>>>(seg_acc.get(), seg_off.get(), (uint32_t)nb); ctx->launches++;
     mark(4);
     msm_reduce_kernel<F><<<(W * T + 127) / 128, 128, 0, st>>>(seg_acc.get(), seg_off.get(), c, W, T, partial.get()); ctx->launches++;
     msm_window_sum_kernel<F><<<W, 32, 0, st>>>(partial.get(), T, win.get()); ctx->launches++;

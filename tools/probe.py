@@ -31,8 +31,9 @@ def timed(fn, reps=3):
 def main():
     max_ntt = int(sys.argv[1]) if len(sys.argv) > 1 else 26
     max_msm = int(sys.argv[2]) if len(sys.argv) > 2 else 24
-    stream = torch.cuda.current_stream().cuda_stream
-    ctx = lib.Context(0, stream)
+    ts = torch.cuda.Stream()
+    torch.cuda.set_stream(ts)             # all torch work and the library share one stream
+    ctx = lib.Context(0, ts.cuda_stream)
     peak, ms = ctx.mad32_peak()
     print(json.dumps({"mad32_peak_per_s": peak, "ms": ms}), flush=True)
     for log_n in range(16, max_ntt + 1, 2 if max_ntt > 20 else 1):
