@@ -1,0 +1,377 @@
+#!/usr/bin/env python
+"""Benchmark of the Groth16 proving path (BASELINE.json metric), one JSON line on stdout.
+
+    python bench.py --gpus N --steps K --warmup W [--impl reference] [--workload NAME]
+
+A step = one partition proof (witness -> 192-byte proof) of a PoRep-C2-shaped synthetic R1CS
+through libb2g16 (hand-written sm_100a kernels behind the C ABI of include/b2g16.h).
+`value` times K proofs with the witness already in HBM; `e2e` times the same through the
+host-buffer entry point b2g16_prove (pinned witness H2D + proof D2H inside the timed region).
+The line also carries the two standalone figures the metric names (G1 MSM Mpts/s, Fr NTT ms)
+with their rooflines, and a CPU baseline (the oracle's OpenMP prover on the box's host cores,
+bounded sample).  `--impl reference` times only that CPU prover (the reference's own
+implementation of this path is absent from its tree: DESIGN.md section 3).
+Under torchrun (N > 1) every rank proves its own partitions (same key, different witness):
+weak scaling, no data-path collective; times are max over ranks.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "crypto3-fil-proofs_b200", "python"), os.path.join(ROOT, "tests")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np
+
+# workload name -> (log_m, challenges per partition, description); n_in = 3 + 18 * challenges
+WORKLOADS = {
+    "c1-2^16": (16, 0, "Groth16 prove, synthetic 2^16-domain R1CS (BASELINE configs[0])"),
+    "porep-c2-2KiB": (22, 2, "PoRep C2 partition, 2 KiB-sector-shaped circuit: domain 2^22, 39 public inputs (BASELINE configs[1])"),
+    "porep-c2-2^24": (24, 18, "PoRep C2 partition shape scaled to a 2^24 domain, 327 public inputs"),
+    "porep-c2-32GiB": (27, 18, "PoRep C2 partition, 32 GiB-sector-shaped circuit: domain 2^27, 327 public inputs (BASELINE configs[4], one partition)"),
+}
+MAD32_PER_G1_POINT = 48000.0      # 16 windows x 10 Fq products x 300 MAD32
+MAD32_PER_G2_POINT = 144000.0
+METRIC = "groth16_c2_partition_prove_s"
+
+
+def n_in_of(workload):
+    log_m, ch, _ = WORKLOADS[workload]
+    return 1 if ch == 0 else 3 + 18 * ch
+
+
+def peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ------------------------------------------------------------------------------- clocks
+CLOCK_QUERY = ("index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,clocks_event_reasons.hw_slowdown,"
+               "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+
+class ClockSampler:
+    def __init__(self, device):
+        self.path = "/tmp/b2g16_clocks_%d_%d.csv" % (os.getpid(), device)
+        self.proc = None
+        try:
+            self.f = open(self.path, "w")
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(device), "--query-gpu=" + CLOCK_QUERY, "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=self.f, stderr=subprocess.DEVNULL)
+        except OSError:
+            self.proc = None
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        self.f.close()
+        sm, smax, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        with open(self.path) as f:
+            for line in f:
+                c = [x.strip() for x in line.split(",")]
+                if len(c) < 9:
+                    continue
+                try:
+                    sm.append(float(c[1])); smax.append(float(c[2]))
+                except ValueError:
+                    continue
+                for nm, v in zip(names, c[5:9]):
+                    if v.lower().startswith("active"):
+                        reasons.add(nm)
+        os.unlink(self.path)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        return {"sm_mhz": float(np.median(sm)), "sm_max_mhz": max(smax), "reasons": sorted(reasons), "samples": len(sm)}
+
+
+# ----------------------------------------------------------------------------- instance
+def build_instance(workload, seed=2026):
+    """Host-side synthetic R1CS (numpy).  Shape: SURVEY 8(d) -- 3 nnz/row in A and B, 1 in C,
+    n_cons = 2^log_m - n_in - 1 (domain exactly 2^log_m)."""
+    from b2g16 import synth
+    log_m = WORKLOADS[workload][0]
+    return synth.SynthR1cs(log_m, n_in_of(workload), seed, n_free=8)
+
+
+def toxic_from_seed(seed):
+    from b2g16 import codec
+    rng = np.random.Generator(np.random.PCG64(seed ^ 0x70C51C))
+    t = codec.random_fr(7, rng)
+    return t[:5], t[5], t[6]
+
+
+class _Cs:
+    """what lib._r1cs_view reads"""
+
+    def __init__(self, s):
+        self.log_m, self.n_in, self.n_aux, self.n_cons = s.log_m, s.n_in, s.n_aux, s.n_cons
+        self.n_vars = s.n_vars
+        self.mats = [s.A, s.B, s.C]
+
+
+def dev_random_fr(torch, n, seed, device):
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    x = torch.randint(0, 256, (n, 32), dtype=torch.uint8, device=device, generator=g)
+    x[:, 31] &= 0x3F                      # < 2^254 < r: canonical, near-uniform (all 16 signed windows populated)
+    return x
+
+
+# ------------------------------------------------------------------------ CPU baseline
+def cpu_prove_sample(workload, sample_log_m, steps=1, warmup=0, seed=2026):
+    """The oracle's OpenMP Groth16 prover (oracle/c/oracle.cpp) on a 2^sample_log_m instance of the
+    same shape, all host threads; returns (seconds per proof scaled linearly to the workload's
+    domain, threads, sample description).  Setup (CPU) is outside the timed region."""
+    from oracle import coracle
+    from b2g16 import synth
+    coracle.build()
+    log_m = WORKLOADS[workload][0]
+    n_in = n_in_of(workload)
+    sample_log_m = min(sample_log_m, log_m)
+    s = synth.SynthR1cs(sample_log_m, n_in, seed, n_free=8)
+    cs = coracle.R1csArrays(s.log_m, s.n_in, s.n_aux, s.A, s.B, s.C)
+    z = coracle.synth_witness(cs, s.z_head, s.n_free)
+    toxic, r, sr = toxic_from_seed(seed)
+    key = coracle.groth16_setup(cs, toxic)
+    times = []
+    for i in range(warmup + steps):
+        t0 = time.perf_counter()
+        proof, _ = coracle.groth16_prove(key, z, r, sr, want_trace=False)
+        dt = time.perf_counter() - t0
+        if i >= warmup:
+            times.append(dt)
+    assert len(proof) == 192
+    scale = float(1 << (log_m - sample_log_m))
+    per = sum(times) / len(times)
+    sample = "oracle C++/OpenMP Groth16 prove at domain 2^%d (%.2f s/proof measured), scaled x%d linearly to 2^%d" % (sample_log_m, per, int(scale), log_m)
+    return per * scale, coracle.threads(), sample, sum(times)
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    sample_log = args.cpu_sample_log_m or (18 if WORKLOADS[args.workload][0] >= 18 else WORKLOADS[args.workload][0])
+    t0 = time.perf_counter()
+    v, threads, sample, timed_s = cpu_prove_sample(args.workload, sample_log, steps=args.steps, warmup=min(args.warmup, 1))
+    line = {
+        "impl": "reference", "metric": METRIC, "value": v, "unit": "s", "n_gpus": args.gpus, "steps": args.steps, "warmup": min(args.warmup, 1),
+        "ms_per_step": 1e3 * timed_s / args.steps, "higher_is_better": False, "scaling": "weak", "vs_baseline": None, "dtype": "u32-limb Montgomery (integer)",
+        "data": "synthetic", "config": {"workload": args.workload, "describe": WORKLOADS[args.workload][2], "log_m": WORKLOADS[args.workload][0], "n_in": n_in_of(args.workload)},
+        "cpu_baseline": {"value": v, "unit": "s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": v, "unit": "s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0, "wall_s": time.perf_counter() - t0,
+        "note": "the reference's own prover sources are absent from its tree (un-vendored crypto3 submodules), so kind=port: the oracle restatement",
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ---------------------------------------------------------------------------- B200 arm
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from b2g16 import codec, lib
+
+    rank, world = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device -- the product path has no CPU fallback (use --impl reference for the CPU prover)")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    ts = torch.cuda.Stream()
+    torch.cuda.set_stream(ts)             # torch work, its events and the library share one stream
+    ctx = lib.Context(local, ts.cuda_stream)
+    hbm_peak, peak_src = peaks()
+
+    def barrier():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+
+    def max_over_ranks(ms):
+        if world == 1:
+            return ms
+        t = torch.tensor([ms], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def timed_region(fn, reps):
+        """barrier + sync, events on the library's stream around `reps` calls, sync + barrier; max over ranks"""
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        barrier()
+        return max_over_ranks(e0.elapsed_time(e1))
+
+    # ---- instance, key (device setup), witness (device), all outside the timed region
+    t_setup = time.perf_counter()
+    log_m = WORKLOADS[args.workload][0]
+    s = build_instance(args.workload)
+    cs = _Cs(s)
+    toxic, r, sr = toxic_from_seed(2026)
+    pk = ctx.pk_generate(cs, toxic)
+    nv = s.n_vars
+    head = s.z_head.copy()
+    if rank:                              # a different witness per rank: fresh inputs and free variables
+        rng = np.random.Generator(np.random.PCG64(9000 + rank))
+        head[1:] = codec.random_fr(head.shape[0] - 1, rng)
+    dz = torch.zeros((nv, 32), dtype=torch.uint8, device=dev)
+    dz[: head.shape[0]] = torch.from_numpy(head).to(dev)
+    ctx.synth_witness(pk, dz.data_ptr(), s.n_free)
+    hz = torch.empty((nv, 32), dtype=torch.uint8, pin_memory=True)
+    hz.copy_(dz)
+    torch.cuda.synchronize()
+    hz_np = hz.numpy()
+    t_setup = time.perf_counter() - t_setup
+
+    proofs = []
+    step_dev = lambda: proofs.append(ctx.prove_device(pk, dz.data_ptr(), r, sr))
+    step_e2e = lambda: proofs.append(ctx.prove(pk, hz_np, r, sr))
+    for _ in range(args.warmup):
+        step_dev()
+    for _ in range(min(args.warmup, 2)):
+        step_e2e()
+    assert len(set(proofs)) == 1 and len(proofs[0]) == 192, "device-resident and host-buffer entry points disagree"
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    l0 = ctx.launches
+    ms = timed_region(step_dev, args.steps)
+    launches = ctx.launches - l0
+    ms_e2e = timed_region(step_e2e, args.steps)
+    clocks = sampler.stop() if sampler else None
+    assert len(set(proofs)) == 1
+
+    # ---- dominant kernel: bucket accumulation of the G1 MSM; roofline on the int32 multiply pipe
+    mad_peak, _ = ctx.mad32_peak()
+    n_h = (1 << log_m) - 1
+    kk = dev_random_fr(torch, n_h, 99, dev)
+    bases = ctx.bases_generate(1, kk.data_ptr(), n_h)
+    del kk
+    sc = dev_random_fr(torch, n_h, 7, dev)
+    out = torch.zeros(192, dtype=torch.uint8, device=dev)
+    ctx.msm_resident_async(bases, sc.data_ptr(), n_h, out.data_ptr())
+    ctx.set_msm_timing(True)
+    acc_ms, tot_ms = [], []
+    for _ in range(3):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record(); ctx.msm_resident_async(bases, sc.data_ptr(), n_h, out.data_ptr()); e1.record()
+        torch.cuda.synchronize()
+        acc_ms.append(ctx.last_msm_timing()["accumulate"]); tot_ms.append(e0.elapsed_time(e1))
+    ctx.set_msm_timing(False)
+    bases.free()
+    del sc
+    acc = sum(acc_ms) / len(acc_ms)
+    achieved = n_h * MAD32_PER_G1_POINT / (acc * 1e-3) / 1e12
+    roofline = {"kernel": "msm_accumulate_kernel<Fq> (bucket accumulation, G1 h-query size)", "bound": "int32-imad", "achieved": achieved,
+                "peak": mad_peak / 1e12, "unit": "TMAD32/s", "frac": achieved / (mad_peak / 1e12), "traffic": None,
+                "launch_ms": acc, "units_per_launch": n_h, "alg_mad32_per_point": MAD32_PER_G1_POINT,
+                "peak_source": "b2g16_measure_mad32_peak (dependency-free mad.wide.u32 loop, this run)",
+                "hbm_view": {"alg_bytes": n_h * 128, "GBps": n_h * 128 / (acc * 1e-3) / 1e9, "peak_GBps": hbm_peak, "peak_source": peak_src},
+                "msm_total_ms": sum(tot_ms) / len(tot_ms)}
+
+    line = {
+        "metric": METRIC, "value": ms / 1e3 / (args.steps * world), "unit": "s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms / args.steps, "higher_is_better": False, "scaling": "weak", "vs_baseline": None,
+        "dtype": "u32-limb Montgomery (integer; Fr 8 limbs, Fq 12 limbs)", "data": "synthetic",
+        "config": {"workload": args.workload, "describe": WORKLOADS[args.workload][2], "log_m": log_m, "n_in": s.n_in, "n_cons": s.n_cons, "n_vars": nv,
+                   "partitions_per_step_per_gpu": 1, "l2": "inputs larger than L2 (key queries %.0f MB, witness %.0f MB per proof)" % (5 * nv * 96 / 1e6, nv * 32 / 1e6),
+                   "parallelism": "one partition per GPU, key replicated, no data-path collective"},
+        "e2e": {"value": ms_e2e / 1e3 / (args.steps * world), "unit": "s", "h2d_bytes_per_step": nv * 32 + 64, "d2h_bytes_per_step": 192 + 672,
+                "ms_per_step": ms_e2e / args.steps, "api": "b2g16_prove (host witness buffer, pinned)"},
+        "gpu_launches": int(launches), "roofline": roofline, "clocks": clocks, "setup_s": t_setup,
+    }
+
+    if rank == 0 and not args.skip_standalone:
+        line["standalone"] = standalone(ctx, torch, dev, args, hbm_peak, peak_src, mad_peak)
+    if rank == 0 and world == 1 and not args.skip_cpu:
+        sample_log = args.cpu_sample_log_m or min(18, log_m)
+        v, threads, sample, _ = cpu_prove_sample(args.workload, sample_log)
+        line["cpu_baseline"] = {"value": v, "unit": "s", "cores": threads, "kind": "port", "sample": sample}
+    pk.free()
+    ctx.close()
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+
+
+def standalone(ctx, torch, dev, args, hbm_peak, peak_src, mad_peak):
+    """The two standalone figures BASELINE.json's metric names: G1 MSM Mpts/s at 2^log_msm and
+    Fr NTT ms at 2^log_ntt, device-resident inputs, best of 3 after a warm-up."""
+    out = {}
+    n = 1 << args.log_msm
+    kk = dev_random_fr(torch, n, 1234, dev)
+    bases = ctx.bases_generate(1, kk.data_ptr(), n)
+    del kk
+    sc = dev_random_fr(torch, n, 4321, dev)
+    res = torch.zeros(192, dtype=torch.uint8, device=dev)
+    ctx.msm_resident_async(bases, sc.data_ptr(), n, res.data_ptr())
+    best = 1e30
+    for _ in range(3):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize(); e0.record(); ctx.msm_resident_async(bases, sc.data_ptr(), n, res.data_ptr()); e1.record(); torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    bases.free()
+    del sc
+    ach = n * MAD32_PER_G1_POINT / (best * 1e-3)
+    out["msm_g1"] = {"log_n": args.log_msm, "ms": best, "Mpts_per_s": n / best / 1e3,
+                     "roofline": {"bound": "int32-imad", "achieved": ach / 1e12, "peak": mad_peak / 1e12, "unit": "TMAD32/s", "frac": ach / mad_peak}}
+    n = 1 << args.log_ntt
+    x = dev_random_fr(torch, n, 77, dev)
+    ctx.ntt_device(x.data_ptr(), args.log_ntt)
+    best = 1e30
+    for _ in range(3):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize(); e0.record(); ctx.ntt_device(x.data_ptr(), args.log_ntt); e1.record(); torch.cuda.synchronize()
+        best = min(best, e0.elapsed_time(e1))
+    del x
+    gbs = 2.0 * n * 32 / (best * 1e-3) / 1e9
+    out["ntt_fr"] = {"log_n": args.log_ntt, "ms": best, "order": "natural in, natural out, canonical bytes both sides",
+                     "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak, "peak_source": peak_src,
+                                  "alg_bytes": 2.0 * n * 32}}
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="porep-c2-2KiB", choices=sorted(WORKLOADS))
+    ap.add_argument("--log-msm", type=int, default=26)
+    ap.add_argument("--log-ntt", type=int, default=27)
+    ap.add_argument("--cpu-sample-log-m", type=int, default=0)
+    ap.add_argument("--skip-standalone", action="store_true")
+    ap.add_argument("--skip-cpu", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "b200":
+        args.warmup = 3
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()
