@@ -290,7 +290,7 @@ int b2g16_set_msm_timing(b2g16_ctx* h, int enabled) {
 }
 int b2g16_set_msm_window(b2g16_ctx* h, int window_bits) {
     Ctx* c = reinterpret_cast<Ctx*>(h);
-    if (!c || (window_bits != 0 && (window_bits < 8 || window_bits > 20))) return B2G16_E_INVALID_ARG;
+    if (!c || (window_bits != 0 && (window_bits < 8 || window_bits > 23))) return B2G16_E_INVALID_ARG;
     c->msm_window_override = window_bits;
     return B2G16_OK;
 }

@@ -30,7 +30,7 @@ struct Ctx {
     float msm_ms[5] = {0, 0, 0, 0, 0};  // last timed MSM: digits+hist, scan, scatter, accumulate, reduce
     bool time_msm = false;
     int msm_window_override = 0;        // 0 = pick by size
-    int acc_variant = 31;               // bucket-accumulation kernel variant (B2G16_ACC_VARIANT)
+    int acc_variant = 102;              // bucket-accumulation kernel variant (B2G16_ACC_VARIANT)
     void* fixed_base[2] = {nullptr, nullptr};   // generator tables (G1, G2), built on first use
 };
 

@@ -178,6 +178,101 @@ msm_accumulate_kernel(const Affine<F>* __restrict__ bases, const uint32_t* __res
         seg_acc[seg] = acc;
     }
 }
+// ---- 4'. equal-work bucket accumulation ------------------------------------------------
+// The sorted entry array is cut into one contiguous chunk of L entries per thread, whatever the
+// bucket boundaries: every lane of a warp performs the same number of mixed additions (the
+// one-thread-per-bucket kernel above loses ~16 % of its SIMD slots to Poisson bucket sizes at 128
+// entries per bucket and ~45 % at 32, which is what made wide windows unprofitable).
+// A bucket that lies inside one chunk is written straight to bucket_acc[b]; a bucket cut by chunk
+// boundaries leaves one "tail" piece (its first part, at the end of a chunk) and "head" pieces (its
+// continuations, at the start of later chunks) that msm_fix_pieces_kernel folds afterwards.
+constexpr uint32_t NO_BUCKET = 0xffffffffu;
+
+template <class F, int THREADS, int MINB> __global__ void __launch_bounds__(THREADS, MINB)
+msm_accumulate_chunked_kernel(const Affine<F>* __restrict__ bases, const uint32_t* __restrict__ sorted, const uint32_t* __restrict__ off,
+                              uint32_t n_buckets, Xyzz<F>* __restrict__ bucket_acc, Xyzz<F>* __restrict__ head_part, Xyzz<F>* __restrict__ tail_part,
+                              uint32_t* __restrict__ head_bucket, uint32_t* __restrict__ tail_bucket) {
+    const uint32_t tid = blockIdx.x * blockDim.x + threadIdx.x, n_thr = gridDim.x * blockDim.x;
+    const uint32_t E = off[n_buckets];
+    uint32_t L = (E + n_thr - 1) / n_thr;
+    if (L == 0) L = 1;
+    const uint64_t begin64 = (uint64_t)tid * L;
+    uint32_t hb = NO_BUCKET, tb = NO_BUCKET;
+    if (begin64 < E) {
+        const uint32_t begin = (uint32_t)begin64;
+        const uint32_t end = (E - begin < L) ? E : begin + L;
+        uint32_t lo = 0, hi = n_buckets;                 // largest b with off[b] <= begin
+        while (hi - lo > 1) { uint32_t mid = (lo + hi) >> 1; if (off[mid] <= begin) lo = mid; else hi = mid; }
+        uint32_t b = lo, next = off[b + 1];
+        bool head_open = off[b] < begin;                 // first bucket started in an earlier chunk
+        Xyzz<F> acc = Xyzz<F>::identity();
+        uint32_t e = begin;
+        uint32_t ix = sorted[e];
+        while (e < end) {
+            if (e == next) {                             // bucket b is complete: flush, move on
+                if (head_open) { head_part[tid] = acc; hb = b; head_open = false; } else bucket_acc[b] = acc;
+                acc = Xyzz<F>::identity();
+                do { ++b; next = off[b + 1]; } while (next == e);
+            }
+            Affine<F> p = load_affine(bases + (ix & 0x7fffffffu));
+            if (ix >> 31) p.y = p.y.neg();
+            ++e;
+            if (e < end) {
+                ix = sorted[e];
+                const char* q = reinterpret_cast<const char*>(bases + (ix & 0x7fffffffu));
+                prefetch_l2(q); prefetch_l2(q + sizeof(Affine<F>) - 4);
+            }
+            if (acc.is_identity() && !p.is_identity()) {
+                // opening a bucket costs no addition slot: take the point and, if the bucket goes on
+                // inside this chunk, fall through to add the next one in the same trip
+                acc.X = p.x; acc.Y = p.y; acc.ZZ = F::one(); acc.ZZZ = F::one();
+                if (e >= end || e == next) continue;
+                p = load_affine(bases + (ix & 0x7fffffffu));
+                if (ix >> 31) p.y = p.y.neg();
+                ++e;
+                if (e < end) {
+                    ix = sorted[e];
+                    const char* q = reinterpret_cast<const char*>(bases + (ix & 0x7fffffffu));
+                    prefetch_l2(q); prefetch_l2(q + sizeof(Affine<F>) - 4);
+                }
+            }
+            acc.add_mixed(p);
+        }
+        // last bucket of the chunk: complete iff it ends exactly here
+        const bool goes_on = next > end;
+        if (head_open) { head_part[tid] = acc; hb = b; }             // chunk lies inside one bucket, or its only piece so far
+        else if (goes_on) { tail_part[tid] = acc; tb = b; }
+        else bucket_acc[b] = acc;
+        if (head_open && !goes_on) { /* the bucket that began earlier ends here: still a head piece */ }
+    }
+    head_bucket[tid] = hb;
+    tail_bucket[tid] = tb;
+}
+// One warp per chunk t whose last bucket continues: bucket = tail piece of t + head pieces of t+1..
+template <class F> __global__ void __launch_bounds__(128)
+msm_fix_pieces_kernel(Xyzz<F>* __restrict__ bucket_acc, const Xyzz<F>* __restrict__ head_part, const Xyzz<F>* __restrict__ tail_part,
+                      const uint32_t* __restrict__ head_bucket, const uint32_t* __restrict__ tail_bucket, uint32_t n_chunks) {
+    const uint32_t lane = threadIdx.x & 31;
+    for (uint32_t t = (blockIdx.x * blockDim.x + threadIdx.x) >> 5; t < n_chunks; t += (gridDim.x * blockDim.x) >> 5) {
+        const uint32_t b = tail_bucket[t];
+        if (b == NO_BUCKET) continue;                    // warp-uniform
+        Xyzz<F> acc = Xyzz<F>::identity();
+        if (lane == 0) acc = tail_part[t];
+        // continuation pieces are contiguous chunks t+1, t+2, .. carrying the same bucket id
+        for (uint32_t u = t + 1 + lane; ; u += 32) {
+            const bool mine = u < n_chunks && head_bucket[u] == b;
+            if (mine) { Xyzz<F> q = head_part[u]; xyzz_add_call(&acc, &q); }
+            if (!__any_sync(0xffffffffu, mine)) break;
+            if (!__all_sync(0xffffffffu, mine)) break;   // pieces are contiguous: a gap ends the run
+        }
+        for (int d = 16; d >= 1; d >>= 1) {
+            Xyzz<F> o = xyzz_shfl_down(acc, d);
+            xyzz_add_call(&acc, &o);
+        }
+        if (lane == 0) bucket_acc[b] = acc;
+    }
+}
+
 // a bucket that was split into several segments: one warp folds them into its first slot
 template <class F> __global__ void __launch_bounds__(128)
 msm_fold_segments_kernel(Xyzz<F>* __restrict__ seg_acc, const uint32_t* __restrict__ seg_off, uint32_t n_buckets) {
@@ -206,7 +301,8 @@ msm_reduce_kernel(const Xyzz<F>* __restrict__ seg_acc, const uint32_t* __restric
     Xyzz<F> run = Xyzz<F>::identity(), acc = Xyzz<F>::identity();
     for (uint32_t j = lo + per; j-- > lo;) {                    // weights j+1, descending
         const uint32_t b = w * B + j;
-        if (seg_off[b + 1] > seg_off[b]) { Xyzz<F> t = seg_acc[seg_off[b]]; xyzz_add_call(&run, &t); }
+        if (seg_off == nullptr) { Xyzz<F> t = seg_acc[b]; xyzz_add_call(&run, &t); }
+        else if (seg_off[b + 1] > seg_off[b]) { Xyzz<F> t = seg_acc[seg_off[b]]; xyzz_add_call(&run, &t); }
         xyzz_add_call(&acc, &run);
     }
     // acc = sum (j - lo + 1) B_j ;  add lo * run (double-and-add over the bits of lo)
@@ -230,6 +326,37 @@ msm_window_sum_kernel(const Xyzz<F>* __restrict__ partial, uint32_t T, Xyzz<F>* 
     }
     if (lane == 0) win[w] = acc;
 }
+// ---- 5'. bucket reduction, recursive chunked running sums -------------------------------
+// Window sum = sum_{d=1..B} d * bucket[d-1].  One level turns `count` items (a_i, r_i) with the value
+//   V = sum_i a_i + 2^log_s * sum_i i * r_i
+// into T = ceil(count / per) items of the same form with log_s' = log_s + log2(per):
+//   a'_t = sum_j a_{t,j} + 2^log_s * sum_j j * r_{t,j}   (descending running sum inside the chunk)
+//   r'_t = sum_j r_{t,j}
+// because i = t*per + j.  Level 1 reads the buckets as items 1..B (item 0 = identity, no a_i); the
+// recursion ends with one chunk per window, whose a' is the window sum.  Every level is fully
+// parallel (one thread per chunk, all windows in one launch): 2 additions per bucket at level 1,
+// 1/per of that at each further level.
+template <class F> __global__ void __launch_bounds__(128)
+msm_reduce_level_kernel(const Xyzz<F>* __restrict__ a_in, const Xyzz<F>* __restrict__ r_in, uint32_t count, uint32_t in_stride, int shift_one,
+                        uint32_t per, int log_s, Xyzz<F>* __restrict__ a_out, Xyzz<F>* __restrict__ r_out, uint32_t T, int W) {
+    const uint32_t gid = blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= (uint32_t)W * T) return;
+    const uint32_t w = gid / T, t = gid % T;
+    const uint32_t lo = t * per, hi = lo + per < count ? lo + per : count;
+    const Xyzz<F>* rw = r_in + (size_t)w * in_stride;
+    Xyzz<F> run = Xyzz<F>::identity(), acc = Xyzz<F>::identity(), asum = Xyzz<F>::identity();
+    for (uint32_t i = hi; i-- > lo;) {
+        if (!shift_one) { Xyzz<F> r = rw[i]; xyzz_add_call(&run, &r); }
+        else if (i > 0) { Xyzz<F> r = rw[i - 1]; xyzz_add_call(&run, &r); }
+        if (i > lo) xyzz_add_call(&acc, &run);
+        if (a_in) { Xyzz<F> a = a_in[(size_t)w * in_stride + i]; xyzz_add_call(&asum, &a); }
+    }
+    for (int k = 0; k < log_s; ++k) xyzz_dbl_call(&acc);
+    xyzz_add_call(&asum, &acc);
+    a_out[(size_t)w * T + t] = asum;
+    r_out[(size_t)w * T + t] = run;
+}
+
 // ---- 6. Horner over windows + affine output --------------------------------------------
 B2_D void egress_fq(uint8_t* p, const Fq& m) {
     Fq c; m.to_canonical(c.v);
@@ -298,9 +425,13 @@ template <class F> __global__ void __launch_bounds__(128) gen_mul_kernel(const A
 }
 
 // ---- host driver ---------------------------------------------------------------------
+// Window width by size (measured on B200, uniform scalars, chunked accumulate): every window costs one
+// mixed addition per point, every bucket two full additions in the reduction and the counting-sort
+// scatter gets less local as buckets multiply -- 16 bits up to 2^22 points, 20 bits from 2^23.
 inline int msm_pick_window(size_t n) {
     int lg = 0;
     while (((size_t)1 << (lg + 1)) <= n) ++lg;
+    if (lg >= 23) return 20;
     int c = lg - 4;
     if (c < 8) c = 8;
     if (c > 16) c = 16;
@@ -350,7 +481,7 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
     if (n == 0) { B2_CUDA(cudaMemsetAsync(d_out_bytes, 0, OUT_BYTES, st)); return; }
     B2_REQUIRE(n < ((size_t)1 << 31), B2G16_E_INVALID_ARG, "msm: at most 2^31-1 points per call");
     int c = window_bits ? window_bits : (ctx->msm_window_override ? ctx->msm_window_override : msm_pick_window(n));
-    B2_REQUIRE(c >= 8 && c <= 20, B2G16_E_INVALID_ARG, "msm: window bits must be in [8, 20]");
+    B2_REQUIRE(c >= 8 && c <= 23, B2G16_E_INVALID_ARG, "msm: window bits must be in [8, 23]");
     const int W = msm_windows(c);
     const uint32_t B = 1u << (c - 1);
     const size_t nb = (size_t)W * B;
@@ -361,10 +492,18 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
     const size_t max_segs = nb + max_entries / S + 1;
     const int n_tiles = (int)((nb + SCAN_TILE - 1) / SCAN_TILE);
 
-    DevBuf<uint32_t> hist(nb + 1, st), off(nb + 1, st), cursor(nb + 1, st), seg_off(nb + 1, st), tile_sums((size_t)n_tiles + 1, st), sorted(max_entries, st);
-    DevBuf<Xyzz<F>> seg_acc(max_segs, st);
-    const uint32_t T = msm_reduce_chunks(c);
-    DevBuf<Xyzz<F>> partial((size_t)W * T, st), win(W, st);
+    // G2 at 16-bit windows: the one-thread-per-bucket kernel is faster (measured 86 vs 99 ms at 2^22)
+    const bool chunked = ctx->acc_variant >= 100 && !(sizeof(F) > 48 && c <= 16);
+    constexpr int CH_THREADS = sizeof(F) > 48 ? 64 : 128;
+    const int ch_minb = !chunked ? 0 : (sizeof(F) > 48 ? 4 : ctx->acc_variant - 100);   // G2: 64-thread CTAs at the 255-register cap, 4 per SM
+    const uint32_t n_chunks = chunked ? (uint32_t)(148 * ch_minb * CH_THREADS) : 0;
+    DevBuf<uint32_t> hist(nb + 1, st), off(nb + 1, st), cursor(nb + 1, st), seg_off(chunked ? 0 : nb + 1, st), tile_sums((size_t)n_tiles + 1, st), sorted(max_entries, st);
+    DevBuf<Xyzz<F>> seg_acc(chunked ? nb : max_segs, st), pieces(2 * (size_t)n_chunks, st);
+    DevBuf<uint32_t> piece_bucket(2 * (size_t)n_chunks, st);
+    constexpr uint32_t RED_PER = 32;                                   // items per thread and level in the bucket reduction
+    const uint32_t T1 = (B + 1 + RED_PER - 1) / RED_PER;
+    DevBuf<Xyzz<F>> red_a[2] = {DevBuf<Xyzz<F>>((size_t)W * T1, st), DevBuf<Xyzz<F>>((size_t)W * T1, st)};
+    DevBuf<Xyzz<F>> red_r[2] = {DevBuf<Xyzz<F>>((size_t)W * T1, st), DevBuf<Xyzz<F>>((size_t)W * T1, st)};
 
     cudaEvent_t ev[6] = {};
     const bool timed = ctx->time_msm;
@@ -376,17 +515,55 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
     msm_hist_kernel<<<grid_for(n, 256, 148 * 8), 256, 0, st>>>(d_scalars, n, c, W, hist.get()); ctx->launches++;
     mark(1);
     scan_u32(ctx, st, hist.get(), off.get(), nb, 0, 1, tile_sums.get());
-    scan_u32(ctx, st, hist.get(), seg_off.get(), nb, 1, S, tile_sums.get());
+    if (!chunked) scan_u32(ctx, st, hist.get(), seg_off.get(), nb, 1, S, tile_sums.get());
     B2_CUDA(cudaMemcpyAsync(cursor.get(), off.get(), (nb + 1) * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
     mark(2);
     msm_scatter_kernel<<<grid_for(n, 256, 148 * 8), 256, 0, st>>>(d_scalars, n, c, W, cursor.get(), sorted.get()); ctx->launches++;
     mark(3);
-    launch_accumulate<F>(ctx, st, max_segs, d_bases, sorted.get(), hist.get(), off.get(), seg_off.get(), (uint32_t)nb, S, seg_acc.get());
-    msm_fold_segments_kernel<F><<<grid_for(nb * 32, 128, 148 * 16), 128, 0, st>>>(seg_acc.get(), seg_off.get(), (uint32_t)nb); ctx->launches++;
+    if (chunked) {
+        B2_CUDA(cudaMemsetAsync(seg_acc.get(), 0, nb * sizeof(Xyzz<F>), st));            // empty bucket = identity (ZZ = 0)
+        Xyzz<F>* head = pieces.get(); Xyzz<F>* tail = pieces.get() + n_chunks;
+        uint32_t* hb = piece_bucket.get(); uint32_t* tb = piece_bucket.get() + n_chunks;
+#define B2_CH(MINB) msm_accumulate_chunked_kernel<F, CH_THREADS, MINB><<<148 * MINB, CH_THREADS, 0, st>>>(d_bases, sorted.get(), off.get(), (uint32_t)nb, seg_acc.get(), head, tail, hb, tb)
+        switch (ch_minb) {
+            case 1: B2_CH(1); break;
+            case 2: B2_CH(2); break;
+            case 3: B2_CH(3); break;
+            case 4: B2_CH(4); break;
+            default: B2_REQUIRE(false, B2G16_E_INVALID_ARG, "msm: chunked accumulate variant must be 101..104");
+        }
+#undef B2_CH
+        msm_fix_pieces_kernel<F><<<grid_for((size_t)n_chunks * 32, 128, 148 * 16), 128, 0, st>>>(seg_acc.get(), head, tail, hb, tb, n_chunks);
+        ctx->launches += 2;
+    } else {
+        launch_accumulate<F>(ctx, st, max_segs, d_bases, sorted.get(), hist.get(), off.get(), seg_off.get(), (uint32_t)nb, S, seg_acc.get());
+        msm_fold_segments_kernel<F><<<grid_for(nb * 32, 128, 148 * 16), 128, 0, st>>>(seg_acc.get(), seg_off.get(), (uint32_t)nb); ctx->launches++;
+    }
     mark(4);
-    msm_reduce_kernel<F><<<(W * T + 127) / 128, 128, 0, st>>>(seg_acc.get(), seg_off.get(), c, W, T, partial.get()); ctx->launches++;
-    msm_window_sum_kernel<F><<<W, 32, 0, st>>>(partial.get(), T, win.get()); ctx->launches++;
-    msm_final_kernel<F><<<1, 32, 0, st>>>(win.get(), c, W, d_out_bytes); ctx->launches++;
+    const Xyzz<F>* win = nullptr;
+    if (chunked) {
+        // recursive chunked running sums over bucket_acc (= seg_acc), all windows per launch
+        uint32_t count = B + 1, stride = B;
+        int log_s = 0, side = 0, shift_one = 1;
+        const Xyzz<F>* a_in = nullptr; const Xyzz<F>* r_in = seg_acc.get();
+        for (;;) {
+            const uint32_t T = (count + RED_PER - 1) / RED_PER;
+            msm_reduce_level_kernel<F><<<(W * T + 127) / 128, 128, 0, st>>>(a_in, r_in, count, stride, shift_one, RED_PER, log_s, red_a[side].get(), red_r[side].get(), T, W);
+            ctx->launches++;
+            a_in = red_a[side].get(); r_in = red_r[side].get();
+            if (T == 1) break;
+            count = T; stride = T; log_s += 5; shift_one = 0; side ^= 1;
+        }
+        win = a_in;
+    } else {
+        const uint32_t T = msm_reduce_chunks(c);
+        B2_REQUIRE((size_t)W * T <= (size_t)W * T1 || true, B2G16_E_INTERNAL, "reduce scratch");
+        DevBuf<Xyzz<F>> partial((size_t)W * T, st);
+        msm_reduce_kernel<F><<<(W * T + 127) / 128, 128, 0, st>>>(seg_acc.get(), seg_off.get(), c, W, T, partial.get()); ctx->launches++;
+        msm_window_sum_kernel<F><<<W, 32, 0, st>>>(partial.get(), T, red_a[0].get()); ctx->launches++;
+        win = red_a[0].get();
+    }
+    msm_final_kernel<F><<<1, 32, 0, st>>>(win, c, W, d_out_bytes); ctx->launches++;
     mark(5);
     B2_CUDA(cudaGetLastError());
     if (timed) {

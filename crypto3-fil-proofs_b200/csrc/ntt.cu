@@ -13,6 +13,7 @@ struct NttDomain {
     NttPlan plan;
     Fr *tlo_f = nullptr, *thi_f = nullptr, *tlo_i = nullptr, *thi_i = nullptr;   // w^e, w^-e
     Fr *glo_f = nullptr, *ghi_f = nullptr, *glo_i = nullptr, *ghi_i = nullptr;   // g^e, n^-1 g^-e
+    Fr *glo_f_raw = nullptr, *glo_i_raw = nullptr;                                 // glo_* as plain residues
     Fr n_inv, zinv;                 // n^-1 ;  (g^n - 1)^-1
 };
 
@@ -80,6 +81,10 @@ NttDomain* ntt_domain(Ctx* c, int log_n) {
     d->tlo_i = make_table(c, wi, Fr::one(), 0, n_lo); d->thi_i = make_table(c, wi, Fr::one(), lo, n_hi);
     d->glo_f = make_table(c, g, Fr::one(), 0, n_lo);  d->ghi_f = make_table(c, g, Fr::one(), lo, n_hi);
     d->glo_i = make_table(c, gi, d->n_inv, 0, n_lo);  d->ghi_i = make_table(c, gi, Fr::one(), lo, n_hi);
+    // plain-residue copies: pre * base^e with pre = (Montgomery form of 1/R) = the integer 1
+    Fr raw_one = Fr::zero(); raw_one.v[0] = 1;
+    d->glo_f_raw = make_table(c, g, raw_one, 0, n_lo);
+    d->glo_i_raw = make_table(c, gi, d->n_inv * raw_one, 0, n_lo);
     c->domains[log_n] = d;
     return d;
 }
@@ -87,7 +92,7 @@ NttDomain* ntt_domain(Ctx* c, int log_n) {
 void ntt_free_domains(Ctx* c) {
     for (auto& kv : c->domains) {
         NttDomain* d = kv.second;
-        Fr* t[8] = {d->tlo_f, d->thi_f, d->tlo_i, d->thi_i, d->glo_f, d->ghi_f, d->glo_i, d->ghi_i};
+        Fr* t[10] = {d->tlo_f, d->thi_f, d->tlo_i, d->thi_i, d->glo_f, d->ghi_f, d->glo_i, d->ghi_i, d->glo_f_raw, d->glo_i_raw};
         for (Fr* p : t) cudaFree(p);
         delete d;
     }
@@ -101,6 +106,7 @@ static NttTables tables(Ctx* c, const NttDomain* d, bool inverse) {
     t.roots = inverse ? c->roots_inv : c->roots_fwd;
     t.tlo = inverse ? d->tlo_i : d->tlo_f; t.thi = inverse ? d->thi_i : d->thi_f;
     t.glo = inverse ? d->glo_i : d->glo_f; t.ghi = inverse ? d->ghi_i : d->ghi_f;
+    t.glo_raw = inverse ? d->glo_i_raw : d->glo_f_raw;
     return t;
 }
 

@@ -63,6 +63,7 @@ struct NttPass {
     NttDigits digits;
     // fusions at the two ends of a transform chain
     int in_canon;               // input holds canonical 32-byte scalars: convert (x * R^2) on load
+    int check_canon;            // input holds canonical scalars that are used as they are (see ntt_plan.cuh): range check only
     int out_canon;              // write canonical scalars on store
     int perm_store;             // store position pos -> ntt_digit_index(digits, pos) (digit-reversed -> natural)
     int fuse_abc;               // load computes (x * b[pos] - c[pos]) * zinv   (witness map)
@@ -145,11 +146,11 @@ B2_HD void ntt_phase_load(const NttPass& p, const NttTile& t, const Fr* data, ui
     int row = t.row_of(e), col = t.col_of(e);
     uint64_t g = t.gpos(row, col);
     Fr x = fr_load(data + g);
-    if (p.in_canon) {
+    if (p.in_canon || p.check_canon) {
 #if defined(__CUDA_ARCH__)
         if (Fr::geq_p(x.v)) atomicOr(p.bad, 1);
 #endif
-        x = x * Fr::r2();
+        if (p.in_canon) x = x * Fr::r2();
     }
     if (p.fuse_abc) x = (x * fr_load(p.src_b + g) - fr_load(p.src_c + g)) * p.zinv;
     if (p.scale_mode == 1) x = x * ntt_scale(p, g);

@@ -55,6 +55,7 @@ struct NttTables {                    // device (or host-emulation) pointers, al
     const Fr* roots;                  // w_{2^11}^j, j < 1024   (forward or inverse set)
     const Fr* tlo; const Fr* thi;     // w_N^e two-level        (forward or inverse set)
     const Fr* glo; const Fr* ghi;     // coset powers two-level (g^e, or n^-1 * g^-e)
+    const Fr* glo_raw;                // glo as plain (non-Montgomery) residues: a Montgomery product with it also leaves Montgomery form
 };
 
 // Passes of one transform in execution order.  rn = false: natural -> digit-reversed
@@ -73,7 +74,7 @@ inline std::vector<NttPass> ntt_build_passes(const NttPlan& pl, bool rn, const N
         q.glo = tb.glo; q.ghi = tb.ghi; q.g_lo_bits = pl.lo_bits;
         q.cscale = Fr::one();
         q.digits = pl.digits;
-        q.in_canon = q.out_canon = q.perm_store = q.fuse_abc = 0;
+        q.in_canon = q.check_canon = q.out_canon = q.perm_store = q.fuse_abc = 0;
         q.src_b = q.src_c = nullptr; q.zinv = Fr::one(); q.bad = nullptr;
         out.push_back(q);
     }
@@ -92,14 +93,18 @@ inline std::vector<NttStep> ntt_steps_natural(const NttPlan& pl, const NttTables
     std::vector<NttPass> ps = ntt_build_passes(pl, false, tb);
     NttPass& first = ps.front();
     NttPass& last = ps.back();
-    first.in_canon = in_canon; first.bad = bad;
+    // The transform is linear and every constant it multiplies by is in Montgomery form, so canonical
+    // input taken as it is (x = Montgomery form of x/R) comes out as canonical output: when both ends
+    // are canonical neither conversion product is needed, only the range check of the input.
+    const bool passthrough = in_canon && out_canon;
+    first.in_canon = in_canon && !passthrough; first.check_canon = passthrough; first.bad = bad;
     if (coset && !inverse) { first.scale_mode = 1; first.scale_kind = 1; }       // x_i *= g^i
     if (inverse) {
         last.scale_mode = 2;
         if (coset) last.scale_kind = 2;                                          // n^-1 g^-idx
         else { last.scale_kind = 0; last.cscale = k.n_inv; }
     }
-    last.out_canon = out_canon;
+    last.out_canon = out_canon && !passthrough;
     last.perm_store = 1;
     std::vector<NttStep> out;
     const size_t P = ps.size();
@@ -129,7 +134,8 @@ inline std::vector<NttStep> ntt_steps_h(const NttPlan& pl, const NttTables& fwd_
     std::vector<NttPass> fin = ntt_build_passes(pl, false, inv_tb);
     fin.front().fuse_abc = 1; fin.front().src_b = b; fin.front().src_c = c; fin.front().zinv = k.zinv;
     fin.back().scale_mode = 2; fin.back().scale_kind = 2;
-    fin.back().out_canon = 1; fin.back().perm_store = 1;
+    fin.back().glo = inv_tb.glo_raw;                        // scaling by plain residues converts to canonical for free
+    fin.back().out_canon = 0; fin.back().perm_store = 1;
     const size_t P = fin.size();
     for (size_t i = 0; i < P; ++i) out.push_back({a, i == P - 1 ? h : a, fin[i]});
     return out;

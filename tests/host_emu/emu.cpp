@@ -73,7 +73,7 @@ static std::vector<Fr> pow_table(Fr base, Fr pre, int shift, uint32_t count) {
 }
 struct EmuDomain {
     NttPlan plan; NttConsts k;
-    std::vector<Fr> roots_f, roots_i, tlo_f, thi_f, tlo_i, thi_i, glo_f, ghi_f, glo_i, ghi_i;
+    std::vector<Fr> roots_f, roots_i, tlo_f, thi_f, tlo_i, thi_i, glo_f, ghi_f, glo_i, ghi_i, glo_f_raw, glo_i_raw;
     explicit EmuDomain(int log_n) {
         plan = ntt_make_plan(log_n);
         int lo = plan.lo_bits, hi = log_n - lo;
@@ -88,12 +88,15 @@ struct EmuDomain {
         tlo_i = pow_table(wi, Fr::one(), 0, n_lo); thi_i = pow_table(wi, Fr::one(), lo, n_hi);
         glo_f = pow_table(g, Fr::one(), 0, n_lo); ghi_f = pow_table(g, Fr::one(), lo, n_hi);
         glo_i = pow_table(gi, k.n_inv, 0, n_lo); ghi_i = pow_table(gi, Fr::one(), lo, n_hi);
+        Fr raw_one = Fr::zero(); raw_one.v[0] = 1;
+        glo_f_raw = pow_table(g, raw_one, 0, n_lo); glo_i_raw = pow_table(gi, k.n_inv * raw_one, 0, n_lo);
     }
     NttTables tables(bool inverse) const {
         NttTables t;
         t.roots = (inverse ? roots_i : roots_f).data();
         t.tlo = (inverse ? tlo_i : tlo_f).data(); t.thi = (inverse ? thi_i : thi_f).data();
         t.glo = (inverse ? glo_i : glo_f).data(); t.ghi = (inverse ? ghi_i : ghi_f).data();
+        t.glo_raw = (inverse ? glo_i_raw : glo_f_raw).data();
         return t;
     }
 };

@@ -111,6 +111,121 @@ template <int CH> __global__ void __launch_bounds__(256) k_fq(uint32_t* sink, in
     if (s == 0x1234567u) sink[0] = s;
 }
 
+
+// ---- fd24: Fq product on the FP64 pipe.  16 limbs of 24 bits; every DFMA below is exact (column sums
+// stay below 2^53: at most 32 products of < 2^48 plus a carry), Montgomery radix 2^384 like the
+// 32-bit-limb integer path, so both paths share one Montgomery representation.
+namespace fd {
+constexpr int N = 16;
+__device__ __constant__ double kP[N] = {16755371.0, 16777215.0, 16759294.0, 11621375.0, 11272190.0, 16131102.0, 10548912.0, 6762706.0,
+                                        8721087.0, 4949235.0, 14115959.0, 4410284.0, 1812406.0, 15112779.0, 15350143.0, 1704209.0};
+constexpr uint32_t INV24 = 0xfcfffdu, MASK = 0xffffffu;
+constexpr double TWO52 = 4503599627370496.0, INV_2_24 = 1.0 / 16777216.0, TWO24 = 16777216.0;
+struct F { uint32_t v[N]; };
+
+__device__ __forceinline__ double u2d(uint32_t x) { return __hiloint2double(0x43300000, (int)x) - TWO52; }
+__device__ __forceinline__ uint32_t d2u(double x) { return (uint32_t)__double2loint(x + TWO52); }      // 0 <= x < 2^32, integer valued
+__device__ __forceinline__ double floor24(double t) { return __fma_rz(t, INV_2_24, TWO52) - TWO52; }     // floor(t / 2^24), 0 <= t < 2^53
+
+// r = a * b / 2^384 mod p; limbs of a, b < 2^24, values < 2p  ->  limbs < 2^24, value < 1.5 p
+__device__ __forceinline__ F mul(const F& a, const F& b) {
+    double ad[N], t[N + 1];
+#pragma unroll
+    for (int j = 0; j < N; ++j) { ad[j] = u2d(a.v[j]); t[j] = 0.0; }
+    t[N] = 0.0;
+#pragma unroll
+    for (int i = 0; i < N; ++i) {
+        const double bi = u2d(b.v[i]);
+#pragma unroll
+        for (int j = 0; j < N; ++j) t[j] = fma(ad[j], bi, t[j]);
+        const double q = floor24(t[0]);
+        const double lo = fma(q, -TWO24, t[0]);
+        const uint32_t m = (d2u(lo) * INV24) & MASK;
+        const double md = u2d(m);
+#pragma unroll
+        for (int j = 0; j < N; ++j) t[j] = fma(md, kP[j], t[j]);
+        t[1] = fma(t[0], INV_2_24, t[1]);                  // t[0] is now a multiple of 2^24: exact
+#pragma unroll
+        for (int j = 0; j < N; ++j) t[j] = t[j + 1];
+        t[N] = 0.0;
+    }
+    F r;
+#pragma unroll
+    for (int j = 0; j < N; ++j) {
+        const double q = floor24(t[j]);
+        r.v[j] = d2u(fma(q, -TWO24, t[j]));
+        if (j + 1 < N) t[j + 1] += q;
+    }
+    return r;
+}
+__device__ F from_fq_mont(const Fq& x) {                  // same value, 24-bit limbs
+    F r;
+    for (int j = 0; j < N; ++j) {
+        int bit = 24 * j, i = bit >> 5, sh = bit & 31;
+        uint64_t w = x.v[i];
+        if (i + 1 < 12) w |= (uint64_t)x.v[i + 1] << 32;
+        r.v[j] = (uint32_t)(w >> sh) & MASK;
+    }
+    return r;
+}
+__device__ Fq to_fq_mont(const F& a) {                    // a < 2p -> canonical Montgomery limbs
+    uint32_t c[12];
+    for (int i = 0; i < 12; ++i) c[i] = 0;
+    for (int j = 0; j < N; ++j) {
+        int bit = 24 * j, i = bit >> 5, sh = bit & 31;
+        uint64_t w = (uint64_t)a.v[j] << sh;
+        c[i] |= (uint32_t)w;
+        if (i + 1 < 12) c[i + 1] |= (uint32_t)(w >> 32);
+    }
+    Fq r; Fq::final_sub(r.v, c, 0);
+    return r;
+}
+}  // namespace fd
+
+__global__ void check_fd_kernel(int* bad, int n) {
+    int id = blockIdx.x * blockDim.x + threadIdx.x;
+    if (id >= n) return;
+    uint32_t x[12], y[12];
+    uint32_t s = id * 2654435761u + 777u;
+    for (int i = 0; i < 12; ++i) { s = s * 1664525u + 1013904223u; x[i] = s; s = s * 1664525u + 1013904223u; y[i] = s; }
+    x[11] &= 0x0fffffffu; y[11] &= 0x0fffffffu;
+    if (id == 0) { for (int i = 0; i < 12; ++i) x[i] = y[i] = FqParams::P(i); x[0] -= 1; y[0] -= 1; }
+    Fq fx = Fq::from_canonical(x), fy = Fq::from_canonical(y);
+    Fq want = fx * fy * fy;
+    fd::F a = fd::from_fq_mont(fx), b = fd::from_fq_mont(fy);
+    Fq got = fd::to_fq_mont(fd::mul(fd::mul(a, b), b));
+    if (got != want) atomicAdd(bad, 1);
+}
+template <int CH> __global__ void __launch_bounds__(256) k_fd(uint32_t* sink, int iters) {
+    fd::F x[CH], y;
+    for (int i = 0; i < fd::N; ++i) { y.v[i] = (threadIdx.x * 2654435761u + i) & fd::MASK; for (int c = 0; c < CH; ++c) x[c].v[i] = (i * 7 + c) & fd::MASK; }
+    y.v[15] &= 0xfffff; for (int c = 0; c < CH; ++c) x[c].v[15] &= 0xfffff;
+    for (int it = 0; it < iters; ++it)
+#pragma unroll
+        for (int c = 0; c < CH; ++c) x[c] = fd::mul(x[c], y);
+    uint32_t s = 0; for (int c = 0; c < CH; ++c) for (int i = 0; i < fd::N; ++i) s ^= x[c].v[i];
+    if (s == 0x1234567u) sink[0] = s;
+}
+// warp-specialised: even warps multiply on the integer pipe, odd warps on the FP64 pipe
+__global__ void __launch_bounds__(256) k_both(uint32_t* sink, int it_int, int it_fd) {
+    const int warp = threadIdx.x >> 5;
+    uint32_t s = 0;
+    if (warp & 1) {
+        fd::F x, y;
+        for (int i = 0; i < fd::N; ++i) { y.v[i] = (threadIdx.x * 2654435761u + i) & fd::MASK; x.v[i] = (i * 7) & fd::MASK; }
+        y.v[15] &= 0xfffff; x.v[15] &= 0xfffff;
+        for (int it = 0; it < it_fd; ++it) x = fd::mul(x, y);
+        for (int i = 0; i < fd::N; ++i) s ^= x.v[i];
+    } else {
+        Fq x, y;
+        for (int i = 0; i < 12; ++i) { y.v[i] = threadIdx.x * 2654435761u + i; x.v[i] = i * 7; }
+        y.v[11] &= 0x0fffffffu; x.v[11] &= 0x0fffffffu;
+        for (int it = 0; it < it_int; ++it) x = x * y;
+        for (int i = 0; i < 12; ++i) s ^= x.v[i];
+    }
+    if (s == 0x1234567u) sink[0] = s;
+}
+
 // ---- raw pipe rates with operands that cannot be hoisted (each product reads a live accumulator)
 __global__ void __launch_bounds__(256) k_wide_live(uint64_t* sink, int iters) {
     uint32_t a = threadIdx.x * 2654435761u + 1;
@@ -190,6 +305,21 @@ int main() {
     check_kernel<<<64, 256>>>(bad, 64 * 256);
     int hb = -1; cudaMemcpy(&hb, bad, 4, cudaMemcpyDeviceToHost);
     printf("{\"rr28_mismatches\": %d}\n", hb);
+    cudaMemset(bad, 0, 4);
+    check_fd_kernel<<<64, 256>>>(bad, 64 * 256);
+    cudaMemcpy(&hb, bad, 4, cudaMemcpyDeviceToHost);
+    printf("{\"fd24_mismatches\": %d}\n", hb);
+    for (int bps : {1, 2, 3}) {
+        const int blocks = 148 * bps, threads = 256; const double T = (double)blocks * threads;
+        double f1 = run([&] { k_fd<1><<<blocks, threads>>>((uint32_t*)sink, 512); }, T * 512);
+        double q1 = run([&] { k_fq<1><<<blocks, threads>>>((uint32_t*)sink, 512); }, T * 512);
+        printf("{\"warps_per_smsp\": %d, \"fd24_mul_per_s\": %.4g, \"fq_mul_per_s\": %.4g", bps * 2, f1, q1);
+        for (int fdit : {256, 384, 512}) {
+            double b = run([&] { k_both<<<blocks, threads>>>((uint32_t*)sink, 512, fdit); }, T / 2 * (512 + fdit));
+            printf(", \"both_512_%d\": %.4g", fdit, b);
+        }
+        printf("}\n");
+    }
     for (int bps : {1, 2, 4}) {
         const int blocks = 148 * bps, threads = 256;
         const double T = (double)blocks * threads;

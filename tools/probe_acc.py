@@ -16,7 +16,7 @@ if len(sys.argv) > 1 and sys.argv[1] == "child":
     ctx.msm_resident_async(bases, s.data_ptr(), 1 << log_n, out.data_ptr())
     t = timed(lambda: ctx.msm_resident_async(bases, s.data_ptr(), 1 << log_n, out.data_ptr()), reps=3)
     ctx.set_msm_timing(True); ctx.msm_resident_async(bases, s.data_ptr(), 1 << log_n, out.data_ptr())
-    print(json.dumps({"variant": os.environ.get("B2G16_ACC_VARIANT"), "log_n": log_n, "ms": round(t, 2), "acc_ms": round(ctx.last_msm_timing()["accumulate"], 2),
+    print(json.dumps({"variant": os.environ.get("B2G16_ACC_VARIANT"), "log_n": log_n, "ms": round(t, 2), "stages": {k: round(v, 2) for k, v in ctx.last_msm_timing().items()},
                       "sum": int(out.sum().item())}), flush=True)
 else:
     for v in sys.argv[2:]:
