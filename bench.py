@@ -222,21 +222,21 @@ def run_b200(args):
         barrier()
         return max_over_ranks(e0.elapsed_time(e1))
 
-    # ---- instance, key (device setup), witness (device), all outside the timed region
+    # ---- instance + key generated on the device (hashed synthetic R1CS, b2g16_pk_generate_synth), witness
+    #      evaluated on the device: all outside the timed region
     t_setup = time.perf_counter()
-    log_m = WORKLOADS[args.workload][0]
-    s = build_instance(args.workload)
-    cs = _Cs(s)
-    toxic, r, sr = toxic_from_seed(2026)
-    pk = ctx.pk_generate(cs, toxic)
-    nv = s.n_vars
-    head = s.z_head.copy()
-    if rank:                              # a different witness per rank: fresh inputs and free variables
-        rng = np.random.Generator(np.random.PCG64(9000 + rank))
-        head[1:] = codec.random_fr(head.shape[0] - 1, rng)
+    log_m, n_in, n_free, seed = WORKLOADS[args.workload][0], n_in_of(args.workload), 8, 2026
+    toxic, r, sr = toxic_from_seed(seed)
+    pk = ctx.pk_generate_synth(log_m, n_in, n_free, seed, toxic)
+    shape = pk.shape()
+    nv = shape["n_vars"]
+    rng = np.random.Generator(np.random.PCG64(9000 + rank))     # a different witness per rank: own inputs and free variables
+    head = codec.random_fr(1 + n_in + n_free, rng)
+    head[0] = 0
+    head[0, 0] = 1
     dz = torch.zeros((nv, 32), dtype=torch.uint8, device=dev)
     dz[: head.shape[0]] = torch.from_numpy(head).to(dev)
-    ctx.synth_witness(pk, dz.data_ptr(), s.n_free)
+    ctx.synth_witness(pk, dz.data_ptr(), n_free)
     hz = torch.empty((nv, 32), dtype=torch.uint8, pin_memory=True)
     hz.copy_(dz)
     torch.cuda.synchronize()
@@ -292,7 +292,7 @@ def run_b200(args):
         "metric": METRIC, "value": ms / 1e3 / (args.steps * world), "unit": "s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": ms / args.steps, "higher_is_better": False, "scaling": "weak", "vs_baseline": None,
         "dtype": "u32-limb Montgomery (integer; Fr 8 limbs, Fq 12 limbs)", "data": "synthetic",
-        "config": {"workload": args.workload, "describe": WORKLOADS[args.workload][2], "log_m": log_m, "n_in": s.n_in, "n_cons": s.n_cons, "n_vars": nv,
+        "config": {"workload": args.workload, "describe": WORKLOADS[args.workload][2], "log_m": log_m, "n_in": n_in, "n_cons": shape["n_cons"], "n_vars": nv,
                    "partitions_per_step_per_gpu": 1, "l2": "inputs larger than L2 (key queries %.0f MB, witness %.0f MB per proof)" % (5 * nv * 96 / 1e6, nv * 32 / 1e6),
                    "parallelism": "one partition per GPU, key replicated, no data-path collective"},
         "e2e": {"value": ms_e2e / 1e3 / (args.steps * world), "unit": "s", "h2d_bytes_per_step": nv * 32 + 64, "d2h_bytes_per_step": 192 + 672,
@@ -300,19 +300,91 @@ def run_b200(args):
         "gpu_launches": int(launches), "roofline": roofline, "clocks": clocks, "setup_s": t_setup,
     }
 
+    pk.free()
+    del dz, hz
     if rank == 0 and not args.skip_standalone:
         line["standalone"] = standalone(ctx, torch, dev, args, hbm_peak, peak_src, mad_peak)
+    if world > 1 and not args.skip_standalone:
+        sh = msm_sharded_bench(ctx, torch, dist, dev, args, rank, world, barrier, max_over_ranks, mad_peak)
+        if rank == 0:
+            line["msm_g1_sharded"] = sh
+    if rank == 0 and world == 1 and not args.skip_32gib and args.workload != "porep-c2-32GiB":
+        line["porep_c2_32GiB_partition"] = big_partition(ctx, torch, dev)
     if rank == 0 and world == 1 and not args.skip_cpu:
         sample_log = args.cpu_sample_log_m or min(18, log_m)
         v, threads, sample, _ = cpu_prove_sample(args.workload, sample_log)
         line["cpu_baseline"] = {"value": v, "unit": "s", "cores": threads, "kind": "port", "sample": sample}
-    pk.free()
     ctx.close()
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
     if rank == 0:
         print(json.dumps(line), flush=True)
+
+
+def msm_sharded_bench(ctx, torch, dist, dev, args, rank, world, barrier, max_over_ranks, mad_peak):
+    """One G1 multiexp of 2^log_msm points sharded by contiguous point range over the ranks (strong
+    scaling): every rank reduces its resident slice to an affine point, the partials are all-gathered
+    over NCCL (96 B per rank) and summed on every rank.  Max over ranks, best of 3."""
+    from b2g16 import dist as bd
+    n = 1 << args.log_msm
+    first, last = bd.shard_range(n, rank, world)
+    cnt = last - first
+    kk = dev_random_fr(torch, cnt, 1234 + rank, dev)
+    bases = ctx.bases_generate(1, kk.data_ptr(), cnt)
+    del kk
+    sc = dev_random_fr(torch, cnt, 4321 + rank, dev)
+    part = torch.zeros(96, dtype=torch.uint8, device=dev)
+    allp = torch.zeros((world, 96), dtype=torch.uint8, device=dev)
+
+    def step():
+        ctx.msm_resident_async(bases, sc.data_ptr(), cnt, part.data_ptr())
+        dist.all_gather_into_tensor(allp, part)
+        return ctx.g1_sum(allp.cpu().numpy())
+    res = step()
+    best = 1e30
+    for _ in range(3):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier(); e0.record(); res = step(); e1.record(); barrier()
+        best = min(best, max_over_ranks(e0.elapsed_time(e1)))
+    bases.free()
+    ach = n * MAD32_PER_G1_POINT / (best * 1e-3)
+    return {"log_n": args.log_msm, "n_gpus": world, "points_per_gpu": cnt, "ms": best, "Mpts_per_s": n / best / 1e3, "scaling": "strong",
+            "collective": "all_gather of %d affine partials (96 B each) over NCCL, then b2g16_g1_sum" % world,
+            "roofline": {"bound": "int32-imad", "achieved": ach / 1e12, "peak": world * mad_peak / 1e12, "unit": "TMAD32/s", "frac": ach / (world * mad_peak)},
+            "result_head": bytes(res[:8]).hex()}
+
+
+def big_partition(ctx, torch, dev, log_m=27, n_in=327, reps=2):
+    """The target of BASELINE.json's north_star: one 32 GiB-sector-shaped PoRep C2 partition (domain 2^27,
+    134,217,400 constraints, 327 public inputs) proved on one GPU with the key resident (~150 GB of HBM).
+    Device-generated instance; best of `reps` device-resident proofs."""
+    from b2g16 import codec
+    seed, n_free = 2027, 8
+    toxic, r, sr = toxic_from_seed(seed)
+    t0 = time.perf_counter()
+    pk = ctx.pk_generate_synth(log_m, n_in, n_free, seed, toxic)
+    shape = pk.shape()
+    rng = np.random.Generator(np.random.PCG64(seed))
+    head = codec.random_fr(1 + n_in + n_free, rng)
+    head[0] = 0
+    head[0, 0] = 1
+    dz = torch.zeros((shape["n_vars"], 32), dtype=torch.uint8, device=dev)
+    dz[: head.shape[0]] = torch.from_numpy(head).to(dev)
+    ctx.synth_witness(pk, dz.data_ptr(), n_free)
+    torch.cuda.synchronize()
+    setup_s = time.perf_counter() - t0
+    times = []
+    for _ in range(reps + 1):                               # first one is the warm-up (domain tables, pool growth)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize(); e0.record(); proof = ctx.prove_device(pk, dz.data_ptr(), r, sr); e1.record(); torch.cuda.synchronize()
+        times.append(e0.elapsed_time(e1) / 1e3)
+    free_b, total_b = torch.cuda.mem_get_info()
+    pk.free()
+    del dz
+    return {"log_m": log_m, "n_cons": shape["n_cons"], "n_in": n_in, "prove_s": min(times[1:]), "all_s": times, "setup_s": setup_s,
+            "hbm_used_GB": (total_b - free_b) / 1e9, "proof_len": len(proof),
+            "parity": "size-independent property: proofs of this shape pass the pairing check (tools/large_proof.py; tests/test_gpu_parity.py::test_large_proof_verifies at 2^20)"}
 
 
 def standalone(ctx, torch, dev, args, hbm_peak, peak_src, mad_peak):
@@ -364,6 +436,7 @@ def main():
     ap.add_argument("--cpu-sample-log-m", type=int, default=0)
     ap.add_argument("--skip-standalone", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")
+    ap.add_argument("--skip-32gib", action="store_true")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3

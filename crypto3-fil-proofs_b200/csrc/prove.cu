@@ -59,6 +59,51 @@ __global__ void __launch_bounds__(256) synth_layer_kernel(DevCsr A, DevCsr B, Fr
     }
 }
 
+
+// ------------------------------------------------- hashed synthetic instance (bench/test support)
+// Same shape as python/b2g16/synth.py (3 non-zeros per row in A and B over variables of earlier
+// layers, C_i = the fresh variable of row i) but every column and coefficient is a counter-based hash
+// of (seed, matrix, row, slot), so the instance can be generated on the device at sizes whose host
+// arrays would not fit (2^27 rows = 33 GB) and regenerated bit-identically in numpy at small sizes
+// (synth.HashedR1cs) for parity against the oracle.
+B2_HD uint64_t synth_mix(uint64_t x) {                       // splitmix64
+    x += 0x9E3779B97F4A7C15ull;
+    x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull;
+    x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+B2_HD uint64_t synth_stream(uint64_t seed, uint64_t tag) { return synth_mix(seed ^ (tag * 0xD6E8FEB86659FD93ull)); }
+constexpr int SYNTH_MAX_LAYERS = 96;
+struct SynthLayers { int n; uint64_t first[SYNTH_MAX_LAYERS + 1]; };     // first row of each layer, first[n] = n_cons
+
+__global__ void __launch_bounds__(256) synth_rows_kernel(uint64_t seed, uint64_t n_cons, uint64_t base_vars, SynthLayers L,
+                                                         uint32_t* __restrict__ a_rp, uint32_t* __restrict__ a_col, Fr* __restrict__ a_val,
+                                                         uint32_t* __restrict__ b_rp, uint32_t* __restrict__ b_col, Fr* __restrict__ b_val,
+                                                         uint32_t* __restrict__ c_rp, uint32_t* __restrict__ c_col, Fr* __restrict__ c_val) {
+    const uint64_t sa = synth_stream(seed, 1), sb = synth_stream(seed, 2), va = synth_stream(seed, 3), vb = synth_stream(seed, 4);
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i <= n_cons; i += (uint64_t)gridDim.x * blockDim.x) {
+        a_rp[i] = (uint32_t)(3 * i); b_rp[i] = (uint32_t)(3 * i); c_rp[i] = (uint32_t)i;
+        if (i == n_cons) break;
+        int lo = 0, hi = L.n;                                // layer of row i: largest l with first[l] <= i
+        while (hi - lo > 1) { int mid = (lo + hi) >> 1; if (L.first[mid] <= i) lo = mid; else hi = mid; }
+        const uint64_t visible = base_vars + L.first[lo];
+        for (int j = 0; j < 3; ++j) {
+            const uint64_t e = 3 * i + j;
+            a_col[e] = (uint32_t)((synth_mix(sa + e) >> 11) % visible);
+            b_col[e] = (uint32_t)((synth_mix(sb + e) >> 11) % visible);
+            uint32_t w[8];
+            for (int k = 0; k < 4; ++k) { uint64_t x = synth_mix(va + 4 * e + k); w[2 * k] = (uint32_t)x; w[2 * k + 1] = (uint32_t)(x >> 32); }
+            w[7] &= 0x3fffffffu;                             // < 2^254 < r
+            fr_store(a_val + e, Fr::from_canonical(w));
+            for (int k = 0; k < 4; ++k) { uint64_t x = synth_mix(vb + 4 * e + k); w[2 * k] = (uint32_t)x; w[2 * k + 1] = (uint32_t)(x >> 32); }
+            w[7] &= 0x3fffffffu;
+            fr_store(b_val + e, Fr::from_canonical(w));
+        }
+        c_col[i] = (uint32_t)(base_vars + i);
+        fr_store(c_val + i, Fr::one());
+    }
+}
+
 // --------------------------------------------------------------- Groth16 setup kernels
 // lag[i] = pref * w^i / (tau - w^i)     (Lagrange basis of the domain at tau)
 __global__ void __launch_bounds__(128) lagrange_kernel(Fr* lag, Fr tau, Fr pref, Fr w, uint64_t m) {
@@ -245,10 +290,14 @@ static void prove_one(Ctx* c, const b2g16_pk* pk, const uint8_t* d_z_canon, cons
     for (int i = 0; i < 4; ++i) B2_CUDA(cudaStreamWaitEvent(c->aux[i], c->ev_fork, 0));
     const uint32_t* zc = reinterpret_cast<const uint32_t*>(d_z_canon);
     uint8_t* o = d_out.get();
-    msm_g2_dev(c, pk->b_g2, zc, nv, o + offsetof(MsmOut, b2), c->aux[0], 0);
-    msm_g1_dev(c, pk->a, zc, nv, o + offsetof(MsmOut, a), c->aux[1], 0);
-    msm_g1_dev(c, pk->b_g1, zc, nv, o + offsetof(MsmOut, b1), c->aux[2], 0);
-    msm_g1_dev(c, pk->l, zc + 8 * (1 + pk->n_in), pk->n_aux, o + offsetof(MsmOut, l), c->aux[3], 0);
+    // above 2^24 the witness MSMs run one after the other on the main stream: each needs ~9 GB of sort
+    // scratch at 2^27 and the integer pipe serialises them anyway; below, they overlap the NTT chain
+    const bool serial = pk->log_m > 24;
+    cudaStream_t s_b2 = serial ? st : c->aux[0], s_a = serial ? st : c->aux[1], s_b1 = serial ? st : c->aux[2], s_l = serial ? st : c->aux[3];
+    msm_g2_dev(c, pk->b_g2, zc, nv, o + offsetof(MsmOut, b2), s_b2, 0);
+    msm_g1_dev(c, pk->a, zc, nv, o + offsetof(MsmOut, a), s_a, 0);
+    msm_g1_dev(c, pk->b_g1, zc, nv, o + offsetof(MsmOut, b1), s_b1, 0);
+    msm_g1_dev(c, pk->l, zc + 8 * (1 + pk->n_in), pk->n_aux, o + offsetof(MsmOut, l), s_l, 0);
     h_from_abc_dev(c, a.get(), b.get(), cc.get(), (int)pk->log_m, h.get(), false, nullptr);
     B2_CUDA(cudaEventRecord(ev[3], st));
     msm_g1_dev(c, pk->h, h.get(), m - 1, o + offsetof(MsmOut, h), st, 0);
@@ -286,6 +335,92 @@ static void prove_one(Ctx* c, const b2g16_pk* pk, const uint8_t* d_z_canon, cons
     for (auto& e : ev) cudaEventDestroy(e);
 }
 
+}  // namespace b2
+
+namespace b2 {
+// Groth16 setup on the device for a key whose constraint system is already resident (pk->A/B/C).
+static void setup_on_device(Ctx* c, b2g16_pk* pk, const uint8_t* toxic, uint8_t* vk_out, DevFlag& bad) {
+        bool ok = true;
+        Fr tx[5];
+        for (int i = 0; i < 5; ++i) tx[i] = host_fr_from_bytes(toxic + 32 * i, &ok);
+        B2_REQUIRE(ok, B2G16_E_NOT_CANONICAL, "toxic waste not canonical");
+        const Fr tau = tx[0], alpha = tx[1], beta = tx[2], gamma = tx[3], delta = tx[4];
+        B2_REQUIRE(!gamma.is_zero() && !delta.is_zero(), B2G16_E_INVALID_ARG, "gamma and delta must be non-zero");
+        cudaStream_t st = c->stream;
+        {
+            const uint64_t m = pk->m, nv = pk->n_vars;
+            // Lagrange basis at tau
+            Fr w = host_root_of_unity((int)pk->log_m);
+            Fr tm = tau; for (uint32_t i = 0; i < pk->log_m; ++i) tm = tm.sqr();
+            const Fr zt = tm - Fr::one();
+            uint32_t mc[8] = {(uint32_t)m, (uint32_t)(m >> 32), 0, 0, 0, 0, 0, 0};
+            const Fr pref = zt * Fr::from_canonical(mc).inv();
+            DevBuf<Fr> lag(m, st), u(nv, st), v(nv, st), ww(nv, st);
+            lagrange_kernel<<<grid_for(m, 128), 128, 0, st>>>(lag.get(), tau, pref, w, m); c->launches++;
+            // u, v, w = A^T lag, B^T lag, C^T lag via a column grouping (counting sort by column)
+            const DevCsr* mats[3] = {&pk->A, &pk->B, &pk->C};
+            Fr* outs[3] = {u.get(), v.get(), ww.get()};
+            const int n_tiles = (int)((nv + SCAN_TILE - 1) / SCAN_TILE);
+            for (int t = 0; t < 3; ++t) {
+                const DevCsr& M = *mats[t];
+                DevBuf<uint32_t> hist(nv + 1, st), off(nv + 1, st), cursor(nv + 1, st), tile_sums((size_t)n_tiles + 1, st), ent_row(M.nnz + 1, st), ent_k(M.nnz + 1, st);
+                B2_CUDA(cudaMemsetAsync(hist.get(), 0, (nv + 1) * sizeof(uint32_t), st));
+                if (M.nnz) { csc_hist_kernel<<<grid_for(M.nnz, 256), 256, 0, st>>>(M.col, M.nnz, hist.get()); c->launches++; }
+                scan_u32(c, st, hist.get(), off.get(), nv, 0, 1, tile_sums.get());
+                B2_CUDA(cudaMemcpyAsync(cursor.get(), off.get(), (nv + 1) * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+                if (M.nnz) { csc_scatter_kernel<<<grid_for(M.n_rows, 256), 256, 0, st>>>(M.row_ptr, M.col, M.n_rows, cursor.get(), ent_row.get(), ent_k.get()); c->launches++; }
+                qap_column_kernel<<<grid_for(nv, 128), 128, 0, st>>>(off.get(), ent_row.get(), ent_k.get(), M.val, lag.get(), nv, pk->n_cons, pk->n_in, t == 0, outs[t]); c->launches++;
+                B2_CUDA(cudaGetLastError());
+            }
+            // scalars of every query (canonical), then fixed-base multiplications
+            DevBuf<uint32_t> su(nv * 8, st), sv(nv * 8, st), sk(nv * 8, st), sh((m ? m : 1) * 8, st);
+            fr_to_bytes_dev(c, u.get(), (uint8_t*)su.get(), nv);
+            fr_to_bytes_dev(c, v.get(), (uint8_t*)sv.get(), nv);
+            const Fr ginv = gamma.inv(), dinv = delta.inv();
+            setup_k_kernel<<<grid_for(nv, 128), 128, 0, st>>>(u.get(), v.get(), ww.get(), alpha, beta, ginv, dinv, nv, pk->n_in, sk.get()); c->launches++;
+            if (m > 1) { setup_h_kernel<<<grid_for(m - 1, 128), 128, 0, st>>>(tau, zt * dinv, m - 1, sh.get()); c->launches++; }
+            B2_CUDA(cudaGetLastError());
+            B2_CUDA(cudaMalloc((void**)&pk->a, (nv + 1) * sizeof(G1Affine)));
+            B2_CUDA(cudaMalloc((void**)&pk->b_g1, (nv + 1) * sizeof(G1Affine)));
+            B2_CUDA(cudaMalloc((void**)&pk->b_g2, (nv + 1) * sizeof(G2Affine)));
+            B2_CUDA(cudaMalloc((void**)&pk->l, (pk->n_aux + 1) * sizeof(G1Affine)));
+            B2_CUDA(cudaMalloc((void**)&pk->h, m * sizeof(G1Affine)));
+            gen_mul_g1_dev(c, su.get(), nv, pk->a);
+            gen_mul_g1_dev(c, sv.get(), nv, pk->b_g1);
+            gen_mul_g2_dev(c, sv.get(), nv, pk->b_g2);
+            gen_mul_g1_dev(c, sk.get() + 8 * (1 + pk->n_in), pk->n_aux, pk->l);
+            gen_mul_g1_dev(c, sh.get(), m - 1, pk->h);
+            // single elements and the verifying key: alpha, beta, delta in G1; beta, gamma, delta in G2; IC
+            const size_t n_ic = pk->n_in + 1;
+            DevBuf<uint32_t> s1(8 * 8, st);
+            uint32_t hs[6][8];
+            alpha.to_canonical(hs[0]); beta.to_canonical(hs[1]); delta.to_canonical(hs[2]); gamma.to_canonical(hs[3]);
+            B2_CUDA(cudaMemcpyAsync(s1.get(), hs, sizeof(uint32_t) * 32, cudaMemcpyHostToDevice, st));
+            DevBuf<G1Affine> e1(3, st), ic(n_ic, st);
+            DevBuf<G2Affine> e2(3, st);
+            gen_mul_g1_dev(c, s1.get(), 3, e1.get());                 // alpha, beta, delta
+            gen_mul_g2_dev(c, s1.get() + 8, 3, e2.get());             // beta, delta, gamma
+            gen_mul_g1_dev(c, sk.get(), n_ic, ic.get());
+            G1Affine h1[3]; G2Affine h2[3];
+            B2_CUDA(cudaMemcpyAsync(h1, e1.get(), sizeof(h1), cudaMemcpyDeviceToHost, st));
+            B2_CUDA(cudaMemcpyAsync(h2, e2.get(), sizeof(h2), cudaMemcpyDeviceToHost, st));
+            std::vector<uint8_t> icb(96 * n_ic);
+            if (vk_out) {
+                DevBuf<uint8_t> raw(96 * n_ic, st);
+                g1_to_bytes_dev(c, ic.get(), raw.get(), n_ic, st);
+                B2_CUDA(cudaMemcpyAsync(icb.data(), raw.get(), 96 * n_ic, cudaMemcpyDeviceToHost, st));
+                B2_CUDA(cudaStreamSynchronize(st));
+            }
+            bad.check("constraint system");
+            pk->alpha_g1 = h1[0]; pk->beta_g1 = h1[1]; pk->delta_g1 = h1[2];
+            pk->beta_g2 = h2[0]; pk->delta_g2 = h2[1];
+            if (vk_out) {
+                host_g1_to_bytes(h1[0], vk_out); host_g2_to_bytes(h2[0], vk_out + 96);
+                host_g2_to_bytes(h2[2], vk_out + 288); host_g2_to_bytes(h2[1], vk_out + 480);
+                memcpy(vk_out + 672, icb.data(), 96 * n_ic);
+            }
+        }
+}
 }  // namespace b2
 
 using namespace b2;
@@ -428,90 +563,58 @@ int b2g16_pk_generate(b2g16_ctx* hctx, const b2g16_r1cs_view* cs, const uint8_t 
     if (!c || !cs || !toxic || !out) return B2G16_E_INVALID_ARG;
     *out = nullptr;
     return guard(c, [&] {
-        bool ok = true;
-        Fr tx[5];
-        for (int i = 0; i < 5; ++i) tx[i] = host_fr_from_bytes(toxic + 32 * i, &ok);
-        B2_REQUIRE(ok, B2G16_E_NOT_CANONICAL, "toxic waste not canonical");
-        const Fr tau = tx[0], alpha = tx[1], beta = tx[2], gamma = tx[3], delta = tx[4];
-        B2_REQUIRE(!gamma.is_zero() && !delta.is_zero(), B2G16_E_INVALID_ARG, "gamma and delta must be non-zero");
-        cudaStream_t st = c->stream;
         DevFlag bad(c);
         b2g16_pk* pk = new_pk_with_cs(c, cs, bad.ptr());
+        try { setup_on_device(c, pk, toxic, vk_out, bad); }
+        catch (...) { cudaStreamSynchronize(c->stream); free_pk(pk); throw; }
+        *out = pk;
+    });
+}
+
+int b2g16_pk_generate_synth(b2g16_ctx* hctx, uint32_t log_m, uint64_t n_in, uint64_t n_free, uint64_t seed, const uint8_t toxic[160],
+                            b2g16_pk** out, uint8_t* vk_out) {
+    Ctx* c = reinterpret_cast<Ctx*>(hctx);
+    if (!c || !toxic || !out || log_m > 28) return B2G16_E_INVALID_ARG;
+    *out = nullptr;
+    return guard(c, [&] {
+        const uint64_t m = 1ull << log_m;
+        B2_REQUIRE(n_in + 2 <= m, B2G16_E_INVALID_ARG, "domain too small for the public inputs");
+        b2g16_pk* pk = new b2g16_pk();
         try {
-            const uint64_t m = pk->m, nv = pk->n_vars;
-            // Lagrange basis at tau
-            Fr w = host_root_of_unity((int)pk->log_m);
-            Fr tm = tau; for (uint32_t i = 0; i < pk->log_m; ++i) tm = tm.sqr();
-            const Fr zt = tm - Fr::one();
-            uint32_t mc[8] = {(uint32_t)m, (uint32_t)(m >> 32), 0, 0, 0, 0, 0, 0};
-            const Fr pref = zt * Fr::from_canonical(mc).inv();
-            DevBuf<Fr> lag(m, st), u(nv, st), v(nv, st), ww(nv, st);
-            lagrange_kernel<<<grid_for(m, 128), 128, 0, st>>>(lag.get(), tau, pref, w, m); c->launches++;
-            // u, v, w = A^T lag, B^T lag, C^T lag via a column grouping (counting sort by column)
-            const DevCsr* mats[3] = {&pk->A, &pk->B, &pk->C};
-            Fr* outs[3] = {u.get(), v.get(), ww.get()};
-            const int n_tiles = (int)((nv + SCAN_TILE - 1) / SCAN_TILE);
+            pk->log_m = log_m; pk->m = m; pk->n_in = n_in; pk->n_cons = m - n_in - 1;      // domain exactly 2^log_m
+            pk->n_aux = n_free + pk->n_cons; pk->n_vars = 1 + n_in + pk->n_aux;
+            B2_REQUIRE(3 * pk->n_cons < (1ull << 32), B2G16_E_INVALID_ARG, "non-zero count must fit 32 bits");
+            SynthLayers L; L.n = 0;
+            const uint64_t base = 1 + n_in + n_free;
+            for (uint64_t row = 0; row < pk->n_cons;) {                                    // same layering as synth.layers()
+                B2_REQUIRE(L.n < SYNTH_MAX_LAYERS, B2G16_E_INTERNAL, "too many layers");
+                L.first[L.n++] = row;
+                uint64_t visible = base + row, size = visible / 2 > 1 ? visible / 2 : 1;
+                row += size < pk->n_cons - row ? size : pk->n_cons - row;
+            }
+            L.first[L.n] = pk->n_cons;
+            DevCsr* M[3] = {&pk->A, &pk->B, &pk->C};
             for (int t = 0; t < 3; ++t) {
-                const DevCsr& M = *mats[t];
-                DevBuf<uint32_t> hist(nv + 1, st), off(nv + 1, st), cursor(nv + 1, st), tile_sums((size_t)n_tiles + 1, st), ent_row(M.nnz + 1, st), ent_k(M.nnz + 1, st);
-                B2_CUDA(cudaMemsetAsync(hist.get(), 0, (nv + 1) * sizeof(uint32_t), st));
-                if (M.nnz) { csc_hist_kernel<<<grid_for(M.nnz, 256), 256, 0, st>>>(M.col, M.nnz, hist.get()); c->launches++; }
-                scan_u32(c, st, hist.get(), off.get(), nv, 0, 1, tile_sums.get());
-                B2_CUDA(cudaMemcpyAsync(cursor.get(), off.get(), (nv + 1) * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
-                if (M.nnz) { csc_scatter_kernel<<<grid_for(M.n_rows, 256), 256, 0, st>>>(M.row_ptr, M.col, M.n_rows, cursor.get(), ent_row.get(), ent_k.get()); c->launches++; }
-                qap_column_kernel<<<grid_for(nv, 128), 128, 0, st>>>(off.get(), ent_row.get(), ent_k.get(), M.val, lag.get(), nv, pk->n_cons, pk->n_in, t == 0, outs[t]); c->launches++;
-                B2_CUDA(cudaGetLastError());
+                M[t]->n_rows = pk->n_cons; M[t]->nnz = (t < 2 ? 3 : 1) * pk->n_cons;
+                B2_CUDA(cudaMalloc((void**)&M[t]->row_ptr, (pk->n_cons + 1) * sizeof(uint32_t)));
+                B2_CUDA(cudaMalloc((void**)&M[t]->col, (M[t]->nnz + 1) * sizeof(uint32_t)));
+                B2_CUDA(cudaMalloc((void**)&M[t]->val, (M[t]->nnz + 1) * sizeof(Fr)));
             }
-            // scalars of every query (canonical), then fixed-base multiplications
-            DevBuf<uint32_t> su(nv * 8, st), sv(nv * 8, st), sk(nv * 8, st), sh((m ? m : 1) * 8, st);
-            fr_to_bytes_dev(c, u.get(), (uint8_t*)su.get(), nv);
-            fr_to_bytes_dev(c, v.get(), (uint8_t*)sv.get(), nv);
-            const Fr ginv = gamma.inv(), dinv = delta.inv();
-            setup_k_kernel<<<grid_for(nv, 128), 128, 0, st>>>(u.get(), v.get(), ww.get(), alpha, beta, ginv, dinv, nv, pk->n_in, sk.get()); c->launches++;
-            if (m > 1) { setup_h_kernel<<<grid_for(m - 1, 128), 128, 0, st>>>(tau, zt * dinv, m - 1, sh.get()); c->launches++; }
+            synth_rows_kernel<<<grid_for(pk->n_cons + 1, 256), 256, 0, c->stream>>>(seed, pk->n_cons, base, L, pk->A.row_ptr, pk->A.col, pk->A.val,
+                                                                                   pk->B.row_ptr, pk->B.col, pk->B.val, pk->C.row_ptr, pk->C.col, pk->C.val);
+            c->launches++;
             B2_CUDA(cudaGetLastError());
-            B2_CUDA(cudaMalloc((void**)&pk->a, (nv + 1) * sizeof(G1Affine)));
-            B2_CUDA(cudaMalloc((void**)&pk->b_g1, (nv + 1) * sizeof(G1Affine)));
-            B2_CUDA(cudaMalloc((void**)&pk->b_g2, (nv + 1) * sizeof(G2Affine)));
-            B2_CUDA(cudaMalloc((void**)&pk->l, (pk->n_aux + 1) * sizeof(G1Affine)));
-            B2_CUDA(cudaMalloc((void**)&pk->h, m * sizeof(G1Affine)));
-            gen_mul_g1_dev(c, su.get(), nv, pk->a);
-            gen_mul_g1_dev(c, sv.get(), nv, pk->b_g1);
-            gen_mul_g2_dev(c, sv.get(), nv, pk->b_g2);
-            gen_mul_g1_dev(c, sk.get() + 8 * (1 + pk->n_in), pk->n_aux, pk->l);
-            gen_mul_g1_dev(c, sh.get(), m - 1, pk->h);
-            // single elements and the verifying key: alpha, beta, delta in G1; beta, gamma, delta in G2; IC
-            const size_t n_ic = pk->n_in + 1;
-            DevBuf<uint32_t> s1(8 * 8, st);
-            uint32_t hs[6][8];
-            alpha.to_canonical(hs[0]); beta.to_canonical(hs[1]); delta.to_canonical(hs[2]); gamma.to_canonical(hs[3]);
-            B2_CUDA(cudaMemcpyAsync(s1.get(), hs, sizeof(uint32_t) * 32, cudaMemcpyHostToDevice, st));
-            DevBuf<G1Affine> e1(3, st), ic(n_ic, st);
-            DevBuf<G2Affine> e2(3, st);
-            gen_mul_g1_dev(c, s1.get(), 3, e1.get());                 // alpha, beta, delta
-            gen_mul_g2_dev(c, s1.get() + 8, 3, e2.get());             // beta, delta, gamma
-            gen_mul_g1_dev(c, sk.get(), n_ic, ic.get());
-            G1Affine h1[3]; G2Affine h2[3];
-            B2_CUDA(cudaMemcpyAsync(h1, e1.get(), sizeof(h1), cudaMemcpyDeviceToHost, st));
-            B2_CUDA(cudaMemcpyAsync(h2, e2.get(), sizeof(h2), cudaMemcpyDeviceToHost, st));
-            std::vector<uint8_t> icb(96 * n_ic);
-            if (vk_out) {
-                DevBuf<uint8_t> raw(96 * n_ic, st);
-                g1_to_bytes_dev(c, ic.get(), raw.get(), n_ic, st);
-                B2_CUDA(cudaMemcpyAsync(icb.data(), raw.get(), 96 * n_ic, cudaMemcpyDeviceToHost, st));
-                B2_CUDA(cudaStreamSynchronize(st));
-            }
-            bad.check("constraint system");
-            pk->alpha_g1 = h1[0]; pk->beta_g1 = h1[1]; pk->delta_g1 = h1[2];
-            pk->beta_g2 = h2[0]; pk->delta_g2 = h2[1];
-            if (vk_out) {
-                host_g1_to_bytes(h1[0], vk_out); host_g2_to_bytes(h2[0], vk_out + 96);
-                host_g2_to_bytes(h2[2], vk_out + 288); host_g2_to_bytes(h2[1], vk_out + 480);
-                memcpy(vk_out + 672, icb.data(), 96 * n_ic);
-            }
+            DevFlag bad(c);
+            setup_on_device(c, pk, toxic, vk_out, bad);
         } catch (...) { cudaStreamSynchronize(c->stream); free_pk(pk); throw; }
         *out = pk;
     });
+}
+
+int b2g16_pk_shape(const b2g16_pk* pk, uint64_t out[5]) {
+    if (!pk || !out) return B2G16_E_INVALID_ARG;
+    out[0] = pk->log_m; out[1] = pk->n_cons; out[2] = pk->n_in; out[3] = pk->n_aux; out[4] = pk->n_vars;
+    return B2G16_OK;
 }
 
 }  // extern "C"

@@ -100,6 +100,11 @@ class ProvingKey:
         self.ctx._chk(load().b2g16_pk_export(self.ctx.h, self.h, which, _p(out), C.c_size_t(out.nbytes)))
         return out
 
+    def shape(self):
+        out = (C.c_uint64 * 5)()
+        self.ctx._chk(load().b2g16_pk_shape(self.h, out))
+        return dict(zip(("log_m", "n_cons", "n_in", "n_aux", "n_vars"), [int(x) for x in out]))
+
     def free(self):
         if self.h:
             load().b2g16_pk_free(self.ctx.h, self.h)
@@ -237,6 +242,14 @@ class Context:
         vk = np.zeros(96 + 3 * 192 + 96 * (cs.n_in + 1), dtype=np.uint8) if want_vk else None
         self._chk(load().b2g16_pk_generate(self.h, C.byref(r1), _p(_u8(toxic)), C.byref(h), _p(vk)))
         pk = ProvingKey(self, h, keep)
+        return (pk, vk) if want_vk else pk
+
+    def pk_generate_synth(self, log_m, n_in, n_free, seed, toxic, want_vk=False):
+        h = C.c_void_p()
+        vk = np.zeros(96 + 3 * 192 + 96 * (n_in + 1), dtype=np.uint8) if want_vk else None
+        self._chk(load().b2g16_pk_generate_synth(self.h, C.c_uint32(log_m), C.c_uint64(n_in), C.c_uint64(n_free), C.c_uint64(seed),
+                                                 _p(_u8(toxic)), C.byref(h), _p(vk)))
+        pk = ProvingKey(self, h)
         return (pk, vk) if want_vk else pk
 
     def prove(self, pk, assignment, r, s, priority=False, trace_m=None):

@@ -123,6 +123,14 @@ int b2g16_pk_free(b2g16_ctx*, b2g16_pk*);
  * (S/core/parameter_cache.hpp:185-200 generates throw-away params the same way).
  * vk_out (optional): alpha_g1(96) beta_g2(192) gamma_g2(192) delta_g2(192) then (n_in+1) IC (96 each). */
 int b2g16_pk_generate(b2g16_ctx*, const b2g16_r1cs_view* cs, const uint8_t toxic[160], b2g16_pk** out, uint8_t* vk_out);
+/* Same, for the hashed synthetic constraint system generated on the device (python/b2g16/synth.py
+ * HashedR1cs regenerates it bit-identically on the host at small sizes): n_cons = 2^log_m - n_in - 1,
+ * n_aux = n_free + n_cons.  Lets 2^27-constraint instances (BASELINE configs 4 and 5) exist without
+ * 33 GB of host arrays.  Bench/test support. */
+int b2g16_pk_generate_synth(b2g16_ctx*, uint32_t log_m, uint64_t n_in, uint64_t n_free, uint64_t seed, const uint8_t toxic[160],
+                            b2g16_pk** out, uint8_t* vk_out);
+/* out = { log_m, n_cons, n_in, n_aux, n_vars } */
+int b2g16_pk_shape(const b2g16_pk*, uint64_t out[5]);
 /* read back one query for parity tests: which = 0 a, 1 b_g1, 2 b_g2, 3 l, 4 h,
  * 5 alpha_g1, 6 beta_g1, 7 delta_g1, 8 beta_g2, 9 delta_g2 */
 int b2g16_pk_export(b2g16_ctx*, const b2g16_pk*, int which, uint8_t* out, size_t out_bytes);

@@ -346,3 +346,58 @@ def test_prove_rejects_non_canonical_witness(ctx, oracle):
         ctx.prove(pk, bad, r, sr)
     assert e.value.code == -2
     pk.free()
+
+
+# ------------------------------------------------ device-generated instances, full-size properties
+@pytest.mark.parametrize("log_m,n_in", [(9, 3), (13, 39)])
+def test_hashed_instance_device_equals_host(ctx, oracle, log_m, n_in):
+    """b2g16_pk_generate_synth builds the hashed synthetic R1CS on the device; synth.HashedR1cs is the
+    numpy mirror.  Same key, same witness, and the proof equals the CPU oracle's."""
+    import torch
+    s = synth.HashedR1cs(log_m, n_in, seed=4100 + log_m)
+    cs = util.oracle_cs(oracle, s)
+    toxic, r, sr = util.toxic_from_seed(4100 + log_m)
+    pk_d, vk_d = ctx.pk_generate_synth(log_m, n_in, s.n_free, 4100 + log_m, toxic, want_vk=True)
+    pk_h, vk_h = ctx.pk_generate(cs, toxic, want_vk=True)
+    assert pk_d.shape() == dict(log_m=log_m, n_cons=s.n_cons, n_in=n_in, n_aux=s.n_aux, n_vars=s.n_vars)
+    assert np.array_equal(vk_d, vk_h)
+    for which, cnt in ((0, s.n_vars), (1, s.n_vars), (2, s.n_vars), (3, s.n_aux), (4, (1 << log_m) - 1)):
+        assert np.array_equal(pk_d.export(which, cnt), pk_h.export(which, cnt)), which
+    z = oracle.synth_witness(cs, s.z_head, s.n_free)
+    dz = torch.zeros((s.n_vars, 32), dtype=torch.uint8, device="cuda")
+    dz[: s.z_head.shape[0]] = torch.from_numpy(s.z_head).cuda()
+    ctx.synth_witness(pk_d, dz.data_ptr(), s.n_free)
+    ctx.synchronize()
+    assert np.array_equal(dz.cpu().numpy(), z)
+    key = oracle.Key(cs)
+    for which, n, cnt in ((0, "a", s.n_vars), (1, "b_g1", s.n_vars), (2, "b_g2", s.n_vars), (3, "l", s.n_aux), (4, "h", (1 << log_m) - 1)):
+        setattr(key, n, pk_d.export(which, cnt))
+    for which, n in ((5, "alpha_g1"), (6, "beta_g1"), (7, "delta_g1"), (8, "beta_g2"), (9, "delta_g2")):
+        setattr(key, n, pk_d.export(which, 1)[0])
+    want = oracle.groth16_prove(key, z, r, sr, want_trace=False)[0]
+    assert ctx.prove_device(pk_d, dz.data_ptr(), r, sr) == want
+    assert util.pairing_verify(oracle, vk_d, z[1:1 + n_in], want)
+    pk_d.free(); pk_h.free()
+
+
+def test_large_proof_verifies(ctx, oracle):
+    """2^20-constraint device-generated instance (PoRep-shaped: 39 public inputs): the proof passes the
+    pairing check, and a proof for a perturbed public input does not -- the prove -> verify round trip
+    of libs/storage/test/porep/stacked/circuit/proof.cpp:257-273 at a size no CPU parity run covers."""
+    import torch
+    log_m, n_in, n_free, seed = 20, 39, 8, 555
+    toxic, r, sr = util.toxic_from_seed(seed)
+    pk, vk = ctx.pk_generate_synth(log_m, n_in, n_free, seed, toxic, want_vk=True)
+    shape = pk.shape()
+    head = synth._hashed_fr(synth._stream(seed, 5), 1 + n_in + n_free).copy()
+    head[0] = 0; head[0, 0] = 1
+    dz = torch.zeros((shape["n_vars"], 32), dtype=torch.uint8, device="cuda")
+    dz[: head.shape[0]] = torch.from_numpy(head).cuda()
+    ctx.synth_witness(pk, dz.data_ptr(), n_free)
+    proof = ctx.prove_device(pk, dz.data_ptr(), r, sr)
+    assert len(proof) == 192
+    pub = head[1:1 + n_in]
+    assert util.pairing_verify(oracle, vk, pub, proof)
+    bad = pub.copy(); bad[3, 0] ^= 1
+    assert not util.pairing_verify(oracle, vk, bad, proof)
+    pk.free()
