@@ -282,7 +282,8 @@ def run_b200(args):
     acc = sum(acc_ms) / len(acc_ms)
     achieved = n_h * MAD32_PER_G1_POINT / (acc * 1e-3) / 1e12
     roofline = {"kernel": "msm_accumulate_kernel<Fq> (bucket accumulation, G1 h-query size)", "bound": "int32-imad", "achieved": achieved,
-                "peak": mad_peak / 1e12, "unit": "TMAD32/s", "frac": achieved / (mad_peak / 1e12), "traffic": None,
+                "peak": mad_peak / 1e12, "unit": "TMAD32/s", "frac": achieved / (mad_peak / 1e12), "traffic": ncu_traffic(log_m),
+                "traffic_note": "DRAM bytes per accumulate launch, ncu --set full of the same kernel at 2^22 (profiles/r01_ncu_full_s13.json); 16 windows x 2^22 gathers of 96-byte points = 6.4 GB is the kernel's own minimum, SURVEY's N*128 B counts one read of the inputs; 384 GB/s = 6 % of HBM, not the bound",
                 "launch_ms": acc, "units_per_launch": n_h, "alg_mad32_per_point": MAD32_PER_G1_POINT,
                 "peak_source": "b2g16_measure_mad32_peak (dependency-free mad.wide.u32 loop, this run)",
                 "hbm_view": {"alg_bytes": n_h * 128, "GBps": n_h * 128 / (acc * 1e-3) / 1e9, "peak_GBps": hbm_peak, "peak_source": peak_src},
@@ -422,6 +423,23 @@ def standalone(ctx, torch, dev, args, hbm_peak, peak_src, mad_peak):
                      "roofline": {"bound": "hbm", "achieved": gbs, "peak": hbm_peak, "unit": "GB/s", "frac": gbs / hbm_peak, "peak_source": peak_src,
                                   "alg_bytes": 2.0 * n * 32}}
     return out
+
+
+def ncu_traffic(log_m):
+    """dram__bytes_read.sum + dram__bytes_write.sum of one accumulate launch from the committed
+    `ncu --set full` capture (profiles/r01_ncu_full_s13.json: G1 MSM at 2^22); null at other sizes."""
+    path = os.path.join(ROOT, "profiles", "r01_ncu_full_s13.json")
+    if log_m != 22 or not os.path.exists(path):
+        return None
+    scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}
+    for l in json.load(open(path))["launches"]:
+        if "msm_accumulate" in l.get("Kernel Name", ""):
+            tot = 0.0
+            for k, v in l.items():
+                if k.startswith("dram__bytes_read.sum") or k.startswith("dram__bytes_write.sum"):
+                    tot += float(v) * scale[k.split("[")[1].rstrip("]")]
+            return tot
+    return None
 
 
 def main():
