@@ -1,0 +1,150 @@
+// Parameter-file and multi-proof byte formats.
+//
+// The reference caches Groth16 parameters on disk as  <cache>/v28-<prefix>-<sha256(id)>.params
+// and the verification key as .vk (libs/storage/.../core/parameter_cache.hpp:50-94,125-153) and
+// memory-maps them through offset tables for h / l / a / b_g1 / b_g2
+// (.../core/crypto/mapped_scheme_params.hpp:52-83).  The serialisers themselves live in the
+// un-vendored crypto3-zk-marshalling module; the layout restated here is the published
+// bellperson `Parameters::write` one that Filecoin's parameter files use:
+//   vk:  alpha_g1(96) beta_g1(96) beta_g2(192) gamma_g2(192) delta_g1(96) delta_g2(192)
+//        u32_be n_ic, n_ic * G1(96)
+//   then five u32_be-length-prefixed arrays: h (G1), l (G1), a (G1), b_g1 (G1), b_g2 (G2)
+// with points uncompressed big-endian (G2 coordinates c1 then c0; bit 6 of byte 0 = infinity).
+// Both this and the C ABI's point format are canonical (non-Montgomery) integers, so conversion
+// is a byte shuffle; range / curve validation happens on the device when the key is loaded.
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#include <new>
+
+#include "../../include/b2g16.h"
+
+namespace {
+
+void be_to_le48(const uint8_t* be, uint8_t* le) { for (int i = 0; i < 48; ++i) le[i] = be[47 - i]; }
+
+// file G1 (x y, BE) -> ABI (x y, LE); infinity -> all zero.  false on a malformed flag byte.
+bool g1_file_to_abi(const uint8_t* f, uint8_t* a) {
+    if (f[0] & 0x80) return false;
+    if (f[0] & 0x40) { memset(a, 0, 96); return true; }
+    be_to_le48(f, a); be_to_le48(f + 48, a + 48); return true;
+}
+void g1_abi_to_file(const uint8_t* a, uint8_t* f) {
+    bool z = true; for (int i = 0; i < 96; ++i) z = z && a[i] == 0;
+    if (z) { memset(f, 0, 96); f[0] = 0x40; return; }
+    be_to_le48(a, f); be_to_le48(a + 48, f + 48);
+}
+// file G2 (x.c1 x.c0 y.c1 y.c0, BE) -> ABI (x.c0 x.c1 y.c0 y.c1, LE)
+bool g2_file_to_abi(const uint8_t* f, uint8_t* a) {
+    if (f[0] & 0x80) return false;
+    if (f[0] & 0x40) { memset(a, 0, 192); return true; }
+    be_to_le48(f, a + 48); be_to_le48(f + 48, a); be_to_le48(f + 96, a + 144); be_to_le48(f + 144, a + 96); return true;
+}
+void g2_abi_to_file(const uint8_t* a, uint8_t* f) {
+    bool z = true; for (int i = 0; i < 192; ++i) z = z && a[i] == 0;
+    if (z) { memset(f, 0, 192); f[0] = 0x40; return; }
+    be_to_le48(a + 48, f); be_to_le48(a, f + 48); be_to_le48(a + 144, f + 96); be_to_le48(a + 96, f + 144);
+}
+
+struct File {
+    FILE* f;
+    explicit File(const char* path, const char* mode) : f(fopen(path, mode)) {}
+    ~File() { if (f) fclose(f); }
+};
+
+bool read_u32_be(FILE* f, uint64_t* v) { uint8_t b[4]; if (fread(b, 1, 4, f) != 4) return false; *v = ((uint32_t)b[0] << 24) | (b[1] << 16) | (b[2] << 8) | b[3]; return true; }
+bool write_u32_be(FILE* f, uint64_t v) { uint8_t b[4] = {(uint8_t)(v >> 24), (uint8_t)(v >> 16), (uint8_t)(v >> 8), (uint8_t)v}; return fwrite(b, 1, 4, f) == 4; }
+
+// one array: n points of `fb` file bytes each -> freshly malloc'ed ABI buffer
+int read_points(FILE* f, uint64_t n, int g2, uint8_t** out) {
+    const size_t sz = g2 ? 192 : 96, CH = 4096;
+    uint8_t* buf = (uint8_t*)malloc(n ? n * sz : 1);
+    if (!buf) return B2G16_E_OOM;
+    uint8_t* tmp = (uint8_t*)malloc(CH * sz);
+    if (!tmp) { free(buf); return B2G16_E_OOM; }
+    int rc = B2G16_OK;
+    for (uint64_t i = 0; i < n && rc == B2G16_OK; i += CH) {
+        const size_t k = (size_t)((n - i < CH) ? n - i : CH);
+        if (fread(tmp, sz, k, f) != k) { rc = B2G16_E_INVALID_ARG; break; }
+        for (size_t j = 0; j < k; ++j) {
+            const bool ok = g2 ? g2_file_to_abi(tmp + j * sz, buf + (i + j) * sz) : g1_file_to_abi(tmp + j * sz, buf + (i + j) * sz);
+            if (!ok) { rc = B2G16_E_NOT_CANONICAL; break; }
+        }
+    }
+    free(tmp);
+    if (rc != B2G16_OK) { free(buf); return rc; }
+    *out = buf;
+    return rc;
+}
+bool write_points(FILE* f, const uint8_t* abi, uint64_t n, int g2) {
+    const size_t sz = g2 ? 192 : 96;
+    uint8_t rec[192];
+    for (uint64_t i = 0; i < n; ++i) {
+        if (g2) g2_abi_to_file(abi + i * sz, rec); else g1_abi_to_file(abi + i * sz, rec);
+        if (fwrite(rec, 1, sz, f) != sz) return false;
+    }
+    return true;
+}
+
+}  // namespace
+
+extern "C" {
+
+int b2g16_params_free(b2g16_params* p) {
+    if (!p) return B2G16_OK;
+    free(p->ic); free(p->h); free(p->l); free(p->a); free(p->b_g1); free(p->b_g2);
+    delete p;
+    return B2G16_OK;
+}
+
+int b2g16_params_read(const char* path, b2g16_params** out) {
+    if (!path || !out) return B2G16_E_INVALID_ARG;
+    *out = nullptr;
+    File fh(path, "rb");
+    if (!fh.f) return B2G16_E_INVALID_ARG;
+    b2g16_params* p = new (std::nothrow) b2g16_params();
+    if (!p) return B2G16_E_OOM;
+    memset(p, 0, sizeof *p);
+    uint8_t hdr[864];
+    int rc = B2G16_OK;
+    if (fread(hdr, 1, sizeof hdr, fh.f) != sizeof hdr) rc = B2G16_E_INVALID_ARG;
+    if (rc == B2G16_OK && !(g1_file_to_abi(hdr, p->alpha_g1) && g1_file_to_abi(hdr + 96, p->beta_g1) && g2_file_to_abi(hdr + 192, p->beta_g2) &&
+                            g2_file_to_abi(hdr + 384, p->gamma_g2) && g1_file_to_abi(hdr + 576, p->delta_g1) && g2_file_to_abi(hdr + 672, p->delta_g2)))
+        rc = B2G16_E_NOT_CANONICAL;
+    struct { uint64_t* n; uint8_t** buf; int g2; } arr[6] = {{&p->n_ic, &p->ic, 0}, {&p->n_h, &p->h, 0}, {&p->n_l, &p->l, 0},
+                                                            {&p->n_a, &p->a, 0}, {&p->n_b_g1, &p->b_g1, 0}, {&p->n_b_g2, &p->b_g2, 1}};
+    for (int i = 0; i < 6 && rc == B2G16_OK; ++i) {
+        if (!read_u32_be(fh.f, arr[i].n)) { rc = B2G16_E_INVALID_ARG; break; }
+        rc = read_points(fh.f, *arr[i].n, arr[i].g2, arr[i].buf);
+    }
+    if (rc != B2G16_OK) { b2g16_params_free(p); return rc; }
+    *out = p;
+    return B2G16_OK;
+}
+
+int b2g16_params_write(const char* path, const b2g16_params* p) {
+    if (!path || !p) return B2G16_E_INVALID_ARG;
+    const uint64_t counts[6] = {p->n_ic, p->n_h, p->n_l, p->n_a, p->n_b_g1, p->n_b_g2};
+    for (uint64_t n : counts) if (n >> 32) return B2G16_E_INVALID_ARG;   // u32 length prefixes
+    File fh(path, "wb");
+    if (!fh.f) return B2G16_E_INVALID_ARG;
+    uint8_t hdr[864];
+    g1_abi_to_file(p->alpha_g1, hdr); g1_abi_to_file(p->beta_g1, hdr + 96); g2_abi_to_file(p->beta_g2, hdr + 192);
+    g2_abi_to_file(p->gamma_g2, hdr + 384); g1_abi_to_file(p->delta_g1, hdr + 576); g2_abi_to_file(p->delta_g2, hdr + 672);
+    bool ok = fwrite(hdr, 1, sizeof hdr, fh.f) == sizeof hdr;
+    const uint8_t* bufs[6] = {p->ic, p->h, p->l, p->a, p->b_g1, p->b_g2};
+    for (int i = 0; i < 6 && ok; ++i) ok = write_u32_be(fh.f, counts[i]) && write_points(fh.f, bufs[i], counts[i], i == 5);
+    return ok ? B2G16_OK : B2G16_E_INTERNAL;
+}
+
+// .vk file = the vk block of a .params file alone (parameter_cache.hpp:56,131-145) -> the layout
+// b2g16_vk_prepare takes: alpha_g1 beta_g2 gamma_g2 delta_g2 ic[]   (672 + 96 n_ic bytes)
+int b2g16_params_vk_bytes(const b2g16_params* p, uint8_t* vk_out, size_t vk_bytes) {
+    if (!p || !vk_out || vk_bytes != 672 + 96 * (size_t)p->n_ic) return B2G16_E_INVALID_ARG;
+    memcpy(vk_out, p->alpha_g1, 96); memcpy(vk_out + 96, p->beta_g2, 192); memcpy(vk_out + 288, p->gamma_g2, 192);
+    memcpy(vk_out + 480, p->delta_g2, 192); memcpy(vk_out + 672, p->ic, 96 * (size_t)p->n_ic);
+    return B2G16_OK;
+}
+
+}  // extern "C"

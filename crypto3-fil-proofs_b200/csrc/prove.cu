@@ -228,10 +228,13 @@ static b2g16_pk* new_pk_with_cs(Ctx* c, const b2g16_r1cs_view* cs, int* d_bad) {
     B2_REQUIRE(cs && cs->log_m <= 30, B2G16_E_INVALID_ARG, "constraint system view");
     const uint64_t m = 1ull << cs->log_m;
     B2_REQUIRE(cs->n_cons + cs->n_in + 1 <= m, B2G16_E_INVALID_ARG, "domain too small: need n_cons + n_in + 1 <= 2^log_m");
-    B2_REQUIRE(cs->A.n_rows == cs->n_cons && cs->B.n_rows == cs->n_cons && cs->C.n_rows == cs->n_cons, B2G16_E_INVALID_ARG, "matrix row counts");
+    // shape-only view (no matrices): the caller will bring a, b, c itself (b2g16_prove_abc)
+    const bool shape_only = !cs->A.row_ptr && !cs->B.row_ptr && !cs->C.row_ptr;
+    B2_REQUIRE(shape_only || (cs->A.n_rows == cs->n_cons && cs->B.n_rows == cs->n_cons && cs->C.n_rows == cs->n_cons), B2G16_E_INVALID_ARG, "matrix row counts");
     b2g16_pk* pk = new b2g16_pk();
     pk->log_m = cs->log_m; pk->m = m; pk->n_cons = cs->n_cons; pk->n_in = cs->n_in; pk->n_aux = cs->n_aux;
     pk->n_vars = 1 + cs->n_in + cs->n_aux;
+    if (shape_only) return pk;
     try {
         load_csr(c, cs->A, pk->n_vars, pk->A, d_bad);
         load_csr(c, cs->B, pk->n_vars, pk->B, d_bad);
@@ -254,8 +257,10 @@ template <class A> static A* upload_points(Ctx* c, const uint8_t* bytes, size_t 
 // ---------------------------------------------------------------------------- the prover
 struct MsmOut { uint8_t a[96], b1[96], l[96], h[96], b2[192]; };
 
+// abc_host: optional {a32, b32, c32} host evaluations supplied by the caller's synthesis (b2g16_prove_abc);
+// otherwise a, b, c come from the key's CSR matrices.
 static void prove_one(Ctx* c, const b2g16_pk* pk, const uint8_t* d_z_canon, const uint8_t* r32, const uint8_t* s32,
-                      uint8_t* proof_out, b2g16_trace* tr) {
+                      uint8_t* proof_out, b2g16_trace* tr, const uint8_t* const* abc_host = nullptr) {
     bool ok = true;
     const Fr r = host_fr_from_bytes(r32, &ok), s = host_fr_from_bytes(s32, &ok);
     B2_REQUIRE(ok, B2G16_E_NOT_CANONICAL, "r / s not canonical");
@@ -271,9 +276,18 @@ static void prove_one(Ctx* c, const b2g16_pk* pk, const uint8_t* d_z_canon, cons
     B2_CUDA(cudaEventRecord(ev[0], st));
     fr_from_bytes_dev(c, d_z_canon, z.get(), nv, bad.ptr());
     B2_CUDA(cudaEventRecord(ev[1], st));
-    abc_spmv_kernel<<<grid_for(m, 256), 256, 0, st>>>(pk->A, pk->B, pk->C, z.get(), pk->n_cons, pk->n_in, m, a.get(), b.get(), cc.get());
-    c->launches++;
-    B2_CUDA(cudaGetLastError());
+    if (abc_host) {
+        Fr* dst[3] = {a.get(), b.get(), cc.get()};
+        for (int i = 0; i < 3; ++i) {                                 // same size: upload, then convert in place
+            B2_CUDA(cudaMemcpyAsync(dst[i], abc_host[i], m * 32, cudaMemcpyHostToDevice, st));
+            fr_from_bytes_dev(c, reinterpret_cast<const uint8_t*>(dst[i]), dst[i], m, bad.ptr());
+        }
+    } else {
+        B2_REQUIRE(pk->A.row_ptr && pk->B.row_ptr && pk->C.row_ptr, B2G16_E_INVALID_ARG, "prove: key was loaded without constraint matrices, use b2g16_prove_abc");
+        abc_spmv_kernel<<<grid_for(m, 256), 256, 0, st>>>(pk->A, pk->B, pk->C, z.get(), pk->n_cons, pk->n_in, m, a.get(), b.get(), cc.get());
+        c->launches++;
+        B2_CUDA(cudaGetLastError());
+    }
     if (tr && (tr->a || tr->b || tr->c)) {
         DevBuf<uint8_t> tmp(m * 32, st);
         uint8_t* dst[3] = {tr->a, tr->b, tr->c};
@@ -515,6 +529,19 @@ int b2g16_prove(b2g16_ctx* hctx, const b2g16_pk* pk, const uint8_t* assignment32
         DevBuf<uint8_t> dz(pk->n_vars * 32, c->stream);
         B2_CUDA(cudaMemcpyAsync(dz.get(), assignment32, pk->n_vars * 32, cudaMemcpyHostToDevice, c->stream));
         prove_one(c, pk, dz.get(), r32, s32, proof_out, trace);
+    });
+}
+
+int b2g16_prove_abc(b2g16_ctx* hctx, const b2g16_pk* pk, const uint8_t* a32, const uint8_t* b32, const uint8_t* c32, const uint8_t* assignment32,
+                    const uint8_t r32[32], const uint8_t s32[32], int priority, uint8_t proof_out[192], b2g16_trace* trace) {
+    (void)priority;
+    Ctx* c = reinterpret_cast<Ctx*>(hctx);
+    if (!c || !pk || !a32 || !b32 || !c32 || !assignment32 || !r32 || !s32 || !proof_out) return B2G16_E_INVALID_ARG;
+    return guard(c, [&] {
+        DevBuf<uint8_t> dz(pk->n_vars * 32, c->stream);
+        B2_CUDA(cudaMemcpyAsync(dz.get(), assignment32, pk->n_vars * 32, cudaMemcpyHostToDevice, c->stream));
+        const uint8_t* abc[3] = {a32, b32, c32};
+        prove_one(c, pk, dz.get(), r32, s32, proof_out, trace, abc);
     });
 }
 

@@ -37,6 +37,70 @@ class PkView(C.Structure):
                [("cs", C.POINTER(R1csView))]
 
 
+class Params(C.Structure):
+    """b2g16_params of include/b2g16.h: a bellperson-layout parameter file in ABI encodings."""
+    _fields_ = [("alpha_g1", C.c_uint8 * 96), ("beta_g1", C.c_uint8 * 96), ("beta_g2", C.c_uint8 * 192), ("gamma_g2", C.c_uint8 * 192),
+                ("delta_g1", C.c_uint8 * 96), ("delta_g2", C.c_uint8 * 192)] + \
+               [(n, C.c_uint64) for n in ("n_ic", "n_h", "n_l", "n_a", "n_b_g1", "n_b_g2")] + \
+               [(n, C.c_void_p) for n in ("ic", "h", "l", "a", "b_g1", "b_g2")]
+
+
+PARAM_ARRAYS = (("ic", 96), ("h", 96), ("l", 96), ("a", 96), ("b_g1", 96), ("b_g2", 192))
+PARAM_POINTS = (("alpha_g1", 96), ("beta_g1", 96), ("beta_g2", 192), ("gamma_g2", 192), ("delta_g1", 96), ("delta_g2", 192))
+
+
+def params_write(path, params):
+    """params: dict of numpy uint8 arrays in ABI encodings, keys alpha_g1 .. delta_g2, ic, h, l, a, b_g1, b_g2."""
+    st, keep = Params(), []
+    for n, w in PARAM_POINTS:
+        C.memmove(getattr(st, n), _p(_u8(params[n])), w)
+    for n, w in PARAM_ARRAYS:
+        arr = _u8(params[n], w)
+        keep.append(arr)
+        setattr(st, "n_" + n, arr.shape[0])
+        setattr(st, n, _p(arr))
+    rc = load().b2g16_params_write(os.fsencode(path), C.byref(st))
+    if rc != 0:
+        raise B2g16Error(rc, "b2g16_params_write(%s)" % path)
+
+
+def params_read(path):
+    """-> dict of numpy arrays (copies; the library's buffers are freed before returning)."""
+    h = C.POINTER(Params)()
+    rc = load().b2g16_params_read(os.fsencode(path), C.byref(h))
+    if rc != 0:
+        raise B2g16Error(rc, "b2g16_params_read(%s)" % path)
+    st, out = h.contents, {}
+    for n, w in PARAM_POINTS:
+        out[n] = np.frombuffer(bytes(getattr(st, n)), dtype=np.uint8).copy()
+    for n, w in PARAM_ARRAYS:
+        cnt = int(getattr(st, "n_" + n))
+        out[n] = np.ctypeslib.as_array(C.cast(getattr(st, n), C.POINTER(C.c_uint8)), shape=(cnt * w,)).reshape(cnt, w).copy() if cnt else np.zeros((0, w), np.uint8)
+    vk = np.zeros(672 + 96 * int(st.n_ic), dtype=np.uint8)
+    rc = load().b2g16_params_vk_bytes(h, _p(vk), C.c_size_t(vk.nbytes))
+    load().b2g16_params_free(h)
+    if rc != 0:
+        raise B2g16Error(rc, "b2g16_params_vk_bytes")
+    out["vk"] = vk
+    return out
+
+
+def proof_decode(proof):
+    a, b, c = np.zeros(96, np.uint8), np.zeros(192, np.uint8), np.zeros(96, np.uint8)
+    rc = load().b2g16_proof_decode(_p(_u8(np.frombuffer(bytes(proof), dtype=np.uint8))), _p(a), _p(b), _p(c))
+    if rc != 0:
+        raise B2g16Error(rc, "malformed proof")
+    return a, b, c
+
+
+def proof_encode(a, b, c):
+    out = np.zeros(192, np.uint8)
+    rc = load().b2g16_proof_encode(_p(_u8(a)), _p(_u8(b)), _p(_u8(c)), _p(out))
+    if rc != 0:
+        raise B2g16Error(rc, "proof_encode: point not canonical / not on curve")
+    return out.tobytes()
+
+
 class Trace(C.Structure):
     _fields_ = [(n, C.c_void_p) for n in ("a", "b", "c", "h", "msm_a", "msm_b1", "msm_l", "msm_h", "msm_b2", "A", "C", "B")] + \
                [("stage_ms", C.c_float * 8)]
@@ -108,6 +172,16 @@ class ProvingKey:
     def free(self):
         if self.h:
             load().b2g16_pk_free(self.ctx.h, self.h)
+            self.h = None
+
+
+class PreparedVk:
+    def __init__(self, ctx, handle, n_ic):
+        self.ctx, self.h, self.n_ic = ctx, handle, n_ic
+
+    def free(self):
+        if self.h:
+            load().b2g16_pvk_free(self.ctx.h, self.h)
             self.h = None
 
 
@@ -269,6 +343,41 @@ class Context:
             return proof.tobytes(), bufs
         return proof.tobytes()
 
+    def prove_abc(self, pk, a, b, c, assignment, r, s, priority=False):
+        """prove from caller-supplied a, b, c evaluations (2^log_m canonical scalars each)"""
+        proof = np.zeros(192, dtype=np.uint8)
+        self._chk(load().b2g16_prove_abc(self.h, pk.h, _p(_u8(a, 32)), _p(_u8(b, 32)), _p(_u8(c, 32)), _p(_u8(assignment, 32)),
+                                         _p(_u8(r)), _p(_u8(s)), int(priority), _p(proof), None))
+        return proof.tobytes()
+
+    # ---- verifier
+    def vk_prepare(self, vk):
+        vk = _u8(vk)
+        n_ic = (vk.size - 672) // 96
+        if vk.size < 768 or 672 + 96 * n_ic != vk.size:
+            raise B2g16Error(-1, "vk must be 672 + 96 * n_ic bytes")
+        h = C.c_void_p()
+        self._chk(load().b2g16_vk_prepare(self.h, _p(vk), C.c_size_t(n_ic), C.byref(h)))
+        return PreparedVk(self, h, n_ic)
+
+    def verify(self, pvk, inputs, proof):
+        x = _u8(inputs, 32)
+        ok = C.c_int(0)
+        self._chk(load().b2g16_verify(self.h, pvk.h, _p(x), C.c_size_t(x.shape[0]), _p(_u8(np.frombuffer(bytes(proof), dtype=np.uint8))), C.byref(ok)))
+        return bool(ok.value)
+
+    def verify_batch(self, pvk, inputs, proofs, rand=None):
+        """inputs: (n_proofs, n_in, 32); proofs: 192 * n_proofs bytes; rand: (n_proofs, 32) or None"""
+        pr = _u8(np.frombuffer(bytes(proofs), dtype=np.uint8))
+        n = pr.size // 192
+        x = _u8(inputs)
+        n_in = pvk.n_ic - 1
+        if x.size != n * n_in * 32:
+            raise B2g16Error(-1, "inputs must hold n_proofs * n_in scalars")
+        ok = C.c_int(0)
+        self._chk(load().b2g16_verify_batch(self.h, pvk.h, _p(x), C.c_size_t(n_in), _p(pr), C.c_size_t(n), _p(_u8(rand)) if rand is not None else None, C.byref(ok)))
+        return bool(ok.value)
+
     def prove_device(self, pk, d_assignment_ptr, r, s, priority=False):
         proof = np.zeros(192, dtype=np.uint8)
         self._chk(load().b2g16_prove_device(self.h, pk.h, C.c_void_p(d_assignment_ptr), _p(_u8(r)), _p(_u8(s)), int(priority), _p(proof), None))
@@ -289,6 +398,8 @@ def _r1cs_view(cs):
     keep = []
     v = R1csView()
     v.log_m, v.n_cons, v.n_in, v.n_aux = cs.log_m, cs.n_cons, cs.n_in, cs.n_aux
+    if getattr(cs, "mats", None) is None:        # shape only: the caller proves with prove_abc
+        return v, keep
     for name, (rp, col, val) in zip("ABC", cs.mats):
         rp = np.ascontiguousarray(rp, dtype=np.uint32)
         col = np.ascontiguousarray(col, dtype=np.uint32)

@@ -160,6 +160,52 @@ int b2g16_prove_device(b2g16_ctx*, const b2g16_pk*, const uint8_t* d_assignment3
 int b2g16_prove_batch(b2g16_ctx*, const b2g16_pk*, const uint8_t* assignments32, size_t n_partitions,
                       const uint8_t* r32s, const uint8_t* s32s, int priority, uint8_t* proofs_out);
 
+/* Same prover when the caller's circuit synthesis already produced the constraint evaluations
+ * (the bellperson-style flow of compound_proof::circuit_proofs, S/core/proof/compound_proof.hpp:127-137:
+ * synthesize -> a, b, c on the domain -> prove): a32 / b32 / c32 are 2^log_m canonical scalars each
+ * (rows >= n_cons must already hold the input-consistency values of SURVEY App. B step 2).
+ * The key may have been loaded with empty matrices (cs->A.row_ptr == NULL). */
+int b2g16_prove_abc(b2g16_ctx*, const b2g16_pk*, const uint8_t* a32, const uint8_t* b32, const uint8_t* c32,
+                    const uint8_t* assignment32, const uint8_t r32[32], const uint8_t s32[32], int priority,
+                    uint8_t proof_out[192], b2g16_trace* trace);
+
+/* ---- verifier: replaces verify<r1cs_gg_ppzksnark>(pvk, primary_input, proof) as reached from
+ *      verify_seal / verify_batch_seal (F/api/seal.hpp:339-395, 409-485) through compound_proof::verify
+ *      (S/core/proof/compound_proof.hpp:97-102).  vk bytes: alpha_g1(96) beta_g2(192) gamma_g2(192)
+ *      delta_g2(192) then n_ic = n_in + 1 IC points (96 each) -- the vk_out layout of b2g16_pk_generate.
+ *      The prepared key caches the alpha/beta Miller value and keeps the IC bases on the device
+ *      (the `pvk` of S/core/crypto/mapped_scheme_params.hpp:61). */
+typedef struct b2g16_pvk b2g16_pvk;
+int b2g16_vk_prepare(b2g16_ctx*, const uint8_t* vk, size_t n_ic, b2g16_pvk** out);
+int b2g16_pvk_free(b2g16_ctx*, b2g16_pvk*);
+/* inputs32: n_in canonical scalars (without the leading ONE).  *ok = 1 accept, 0 reject (a malformed
+ * proof is a reject, not an error). */
+int b2g16_verify(b2g16_ctx*, const b2g16_pvk*, const uint8_t* inputs32, size_t n_in, const uint8_t proof[192], int* ok);
+/* n_proofs proofs (192 B each) with n_in inputs each, one random linear combination, one final
+ * exponentiation.  rand32: n_proofs canonical scalars, or NULL to draw them inside. */
+int b2g16_verify_batch(b2g16_ctx*, const b2g16_pvk*, const uint8_t* inputs32, size_t n_in, const uint8_t* proofs,
+                       size_t n_proofs, const uint8_t* rand32, int* ok);
+/* 192-byte proof (F/constants.hpp:93: compressed A(48) B(96) C(48)) <-> ABI affine points; decode
+ * validates the encoding, the curve equation and prime-order subgroup membership. */
+int b2g16_proof_decode(const uint8_t proof[192], uint8_t a96[96], uint8_t b192[192], uint8_t c96[96]);
+int b2g16_proof_encode(const uint8_t a96[96], const uint8_t b192[192], const uint8_t c96[96], uint8_t proof[192]);
+
+/* ---- parameter files: the `.params` / `.vk` cache entries of S/core/parameter_cache.hpp:50-94,125-153
+ *      and the arrays S/core/crypto/mapped_scheme_params.hpp:65-81 indexes, in the bellperson
+ *      Parameters::write layout.  Host-only byte shuffles; points arrive in the ABI
+ *      encoding and are validated when handed to b2g16_pk_load / b2g16_vk_prepare. */
+typedef struct {
+    uint8_t alpha_g1[96], beta_g1[96], beta_g2[192], gamma_g2[192], delta_g1[96], delta_g2[192];
+    uint64_t n_ic, n_h, n_l, n_a, n_b_g1, n_b_g2;
+    uint8_t *ic, *h, *l, *a, *b_g1; /* G1, 96 B each  */
+    uint8_t* b_g2;                  /* G2, 192 B each */
+} b2g16_params;
+int b2g16_params_read(const char* path, b2g16_params** out); /* buffers owned by the library */
+int b2g16_params_free(b2g16_params*);
+int b2g16_params_write(const char* path, const b2g16_params*);
+/* vk block in the b2g16_vk_prepare layout; vk_bytes must be 672 + 96 * n_ic */
+int b2g16_params_vk_bytes(const b2g16_params*, uint8_t* vk_out, size_t vk_bytes);
+
 /* ---- synthetic-instance support (bench/test): evaluate one layer of a forward-built R1CS on
  *      the device: for rows [row0,row1): z[out_base + i] = (A_i . z) * (B_i . z).  d_z canonical. */
 int b2g16_synth_witness(b2g16_ctx*, const b2g16_pk*, uint8_t* d_assignment32, uint64_t n_free);
