@@ -309,6 +309,10 @@ def run_b200(args):
         sh = msm_sharded_bench(ctx, torch, dist, dev, args, rank, world, barrier, max_over_ranks, mad_peak)
         if rank == 0:
             line["msm_g1_sharded"] = sh
+        if world in (2, 4, 8):
+            shn = ntt_sharded_bench(ctx, torch, dist, dev, args, rank, world, barrier, max_over_ranks, hbm_peak)
+            if rank == 0:
+                line["ntt_fr_sharded"] = shn
     if rank == 0 and world == 1 and not args.skip_32gib and args.workload != "porep-c2-32GiB":
         line["porep_c2_32GiB_partition"] = big_partition(ctx, torch, dev)
     if rank == 0 and world == 1 and not args.skip_cpu:
@@ -354,6 +358,33 @@ def msm_sharded_bench(ctx, torch, dist, dev, args, rank, world, barrier, max_ove
             "collective": "all_gather of %d affine partials (96 B each) over NCCL, then b2g16_g1_sum" % world,
             "roofline": {"bound": "int32-imad", "achieved": ach / 1e12, "peak": world * mad_peak / 1e12, "unit": "TMAD32/s", "frac": ach / (world * mad_peak)},
             "result_head": bytes(res[:8]).hex()}
+
+
+def ntt_sharded_bench(ctx, torch, dist, dev, args, rank, world, barrier, max_over_ranks, hbm_peak):
+    """One Fr transform of 2^log_ntt elements sharded over the ranks (strong scaling): rank r holds the
+    block [r M, (r+1) M); two all-to-all exchanges around the cross-rank step + the local size-M transform
+    give the spectrum in cyclic order, a third exchange + transpose the natural block order (SURVEY 8e row 3,
+    b2g16.dist.ntt_sharded).  Max over ranks, best of 3; forward followed by inverse must return the input."""
+    from b2g16 import dist as bd
+    log_n = args.log_ntt
+    M = (1 << log_n) // world
+    ops = bd.DeviceNttOps(ctx)
+    x = dev_random_fr(torch, M, 777 + rank, dev)
+    out = {"log_n": log_n, "n_gpus": world, "elements_per_gpu": M, "scaling": "strong",
+           "collective": "all_to_all_single over NCCL: %d exchanges of %.0f MB per rank (natural order), 2 (cyclic order)" % (3, M * 32 * (world - 1) / world / 1e6)}
+    for order in ("natural", "cyclic"):
+        spec = bd.ntt_sharded(ops, x, log_n, order=order)
+        back = bd.ntt_sharded(ops, spec, log_n, inverse=True, order=order)
+        assert bool(torch.equal(back, x)), "sharded forward + inverse transform is not the identity"
+        best = 1e30
+        for _ in range(3):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier(); e0.record(); spec = bd.ntt_sharded(ops, x, log_n, order=order); e1.record(); barrier()
+            best = min(best, max_over_ranks(e0.elapsed_time(e1)))
+        gbps = 2.0 * (1 << log_n) * 32 / (best * 1e-3) / 1e9
+        out[order] = {"ms": best, "roofline": {"bound": "hbm", "achieved": gbps, "peak": world * hbm_peak, "unit": "GB/s", "frac": gbps / (world * hbm_peak)}}
+        del spec, back
+    return out
 
 
 def big_partition(ctx, torch, dev, log_m=27, n_in=327, reps=2):

@@ -219,6 +219,32 @@ int b2g16_ntt_device(b2g16_ctx* h, uint8_t* d_fr32_inout, unsigned log_n, int in
         bad.check("scalars");
     });
 }
+// ---- one transform sharded over 2^log_g ranks: the per-rank device steps between the all-to-all
+//      exchanges that python/b2g16/dist.py (or any NCCL host) performs.  All buffers hold canonical scalars.
+int b2g16_ntt_cross_device(b2g16_ctx* h, const uint8_t* d_in, uint8_t* d_out, unsigned log_n, unsigned log_g, unsigned chunk, int inverse, int coset) {
+    Ctx* c = reinterpret_cast<Ctx*>(h);
+    if (!c || !d_in || !d_out || d_in == d_out) return B2G16_E_INVALID_ARG;
+    return guard(c, [&] {
+        DevFlag bad(c);
+        ntt_cross_dev(c, reinterpret_cast<const Fr*>(d_in), reinterpret_cast<Fr*>(d_out), (int)log_n, (int)log_g, chunk, inverse != 0, coset != 0, bad.ptr());
+        bad.check("scalars");
+    });
+}
+int b2g16_fr_coset_scale_device(b2g16_ctx* h, uint8_t* d_fr32_inout, size_t count, unsigned log_n, uint64_t offset, int inverse) {
+    Ctx* c = reinterpret_cast<Ctx*>(h);
+    if (!c || (count && !d_fr32_inout) || log_n > 30) return B2G16_E_INVALID_ARG;
+    return guard(c, [&] {
+        DevFlag bad(c);
+        fr_coset_scale_dev(c, reinterpret_cast<Fr*>(d_fr32_inout), count, (int)log_n, offset, inverse != 0, bad.ptr());
+        bad.check("scalars");
+    });
+}
+int b2g16_fr_transpose_device(b2g16_ctx* h, const uint8_t* d_in, uint8_t* d_out, size_t rows, size_t cols) {
+    Ctx* c = reinterpret_cast<Ctx*>(h);
+    if (!c || !d_in || !d_out || d_in == d_out) return B2G16_E_INVALID_ARG;
+    return guard(c, [&] { fr_transpose_dev(c, reinterpret_cast<const Fr*>(d_in), reinterpret_cast<Fr*>(d_out), rows, cols); });
+}
+
 int b2g16_ntt(b2g16_ctx* h, uint8_t* fr32_inout, unsigned log_n, int inverse, int coset) {
     Ctx* c = reinterpret_cast<Ctx*>(h);
     if (!c || !fr32_inout || log_n > 30) return B2G16_E_INVALID_ARG;

@@ -145,4 +145,132 @@ void h_from_abc_dev(Ctx* c, Fr* d_a, Fr* d_b, Fr* d_c, int log_m, uint32_t* d_h_
         launch_pass(c, s.src, s.dst, s.pass);
 }
 
+// ------------------------------------------------------------------ distributed transform
+// One transform of size N = 2^log_n over G = 2^log_g ranks, rank r holding x[r M .. (r+1) M),
+// M = N / G.  With n = r M + j and k = k1 + G k2:
+//     X[k1 + G k2] = sum_j w_M^(j k2) [ w_N^(j k1) sum_r w_G^(r k1) x[r M + j] ]
+// so the only cross-rank arithmetic is a G-point transform per column j followed by the
+// twiddle w_N^(j k1); everything else is the ordinary local transform of size M.  The host
+// side (python/b2g16/dist.py) moves the data with all-to-all exchanges so that a rank holds,
+// for its chunk of M/G columns, the G values of every column: a G x (M/G) row-major matrix.
+// This kernel does the per-column work on that matrix, one thread per column, operands in
+// registers.  Forward: G-point DIF, then twiddles.  Inverse: twiddles (inverse roots), then
+// the inverse G-point transform, times `scale`.  Data stays in canonical form throughout
+// (the transform is linear and every constant is in Montgomery form; ntt_plan.cuh).
+struct CrossRoots { Fr w[4]; };       // w_G^i (forward or inverse), i < G/2, G <= 8
+
+template <int LOG_G> __global__ void __launch_bounds__(128)
+ntt_cross_kernel(const Fr* __restrict__ in, Fr* __restrict__ out, uint64_t cols, uint64_t col0, const Fr* __restrict__ tlo,
+                 const Fr* __restrict__ thi, int lo_bits, CrossRoots roots, Fr scale, int inverse, int use_scale, int* bad) {
+    constexpr int G = 1 << LOG_G;
+    for (uint64_t jj = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; jj < cols; jj += (uint64_t)gridDim.x * blockDim.x) {
+        Fr v[G];
+#pragma unroll
+        for (int r = 0; r < G; ++r) {
+            v[r] = fr_load(in + (uint64_t)r * cols + jj);
+            if (bad && Fr::geq_p(v[r].v)) atomicOr(bad, 1);
+        }
+        const uint64_t j = col0 + jj;                               // global column: exponent of the twiddle base
+        const uint32_t lo = (uint32_t)(j & ((1ull << lo_bits) - 1)), hi = (uint32_t)(j >> lo_bits);
+        Fr t = fr_load(tlo + lo);
+        if (hi) t = t * fr_load(thi + hi);                          // w_N^(+-j)
+        if (inverse) {                                              // v[k1] *= w_N^(-j k1), with the overall scale folded in
+            Fr p = scale;
+            if (use_scale) v[0] = v[0] * p;
+#pragma unroll
+            for (int k = 1; k < G; ++k) { p = (k == 1 && !use_scale) ? t : p * t; v[k] = v[k] * p; }
+        }
+        // G-point radix-2 DIF in registers: natural in, bit-reversed out
+#pragma unroll
+        for (int s = LOG_G - 1; s >= 0; --s) {
+            const int h = 1 << s;
+#pragma unroll
+            for (int b = 0; b < G / 2; ++b) {
+                const int i0 = ((b >> s) << (s + 1)) | (b & (h - 1)), i1 = i0 + h;
+                const int e = (b & (h - 1)) << (LOG_G - 1 - s);    // w_G^e
+                Fr u = v[i0], w = v[i1];
+                v[i0] = u + w;
+                Fr d = u - w;
+                v[i1] = e ? d * roots.w[e] : d;
+            }
+        }
+        if (!inverse) {                                             // y[k1] * w_N^(j k1)
+            Fr p = t;
+#pragma unroll
+            for (int k = 1; k < G; ++k) {
+                int src = 0;
+#pragma unroll
+                for (int bit = 0; bit < LOG_G; ++bit) src |= ((k >> bit) & 1) << (LOG_G - 1 - bit);
+                v[src] = v[src] * p;
+                if (k + 1 < G) p = p * t;
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < G; ++k) {
+            int src = 0;
+#pragma unroll
+            for (int bit = 0; bit < LOG_G; ++bit) src |= ((k >> bit) & 1) << (LOG_G - 1 - bit);
+            fr_store(out + (uint64_t)k * cols + jj, v[src]);
+        }
+    }
+}
+
+// data[i] *= table power of g at global exponent offset + i (coset shift of a rank's block)
+__global__ void __launch_bounds__(256) fr_coset_scale_kernel(Fr* data, uint64_t count, uint64_t offset, const Fr* __restrict__ glo,
+                                                             const Fr* __restrict__ ghi, int lo_bits, int* bad) {
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < count; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t e = offset + i;
+        const uint32_t lo = (uint32_t)(e & ((1ull << lo_bits) - 1)), hi = (uint32_t)(e >> lo_bits);
+        Fr t = fr_load(glo + lo);
+        if (hi) t = t * fr_load(ghi + hi);
+        Fr x = fr_load(data + i);
+        if (bad && Fr::geq_p(x.v)) atomicOr(bad, 1);
+        fr_store(data + i, x * t);
+    }
+}
+// out[c * rows + r] = in[r * cols + c]   (32-byte elements)
+__global__ void __launch_bounds__(256) fr_transpose_kernel(const Fr* __restrict__ in, Fr* __restrict__ out, uint64_t rows, uint64_t cols) {
+    const uint64_t n = rows * cols;
+    for (uint64_t i = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < n; i += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t r = i / cols, c = i % cols;
+        fr_store(out + c * rows + r, fr_load(in + i));
+    }
+}
+
+void ntt_cross_dev(Ctx* c, const Fr* d_in, Fr* d_out, int log_n, int log_g, uint64_t chunk, bool inverse, bool coset, int* d_bad) {
+    B2_REQUIRE(log_g >= 1 && log_g <= 3, B2G16_E_INVALID_ARG, "distributed ntt: 2, 4 or 8 ranks");
+    B2_REQUIRE(log_n >= 2 * log_g && log_n <= 30, B2G16_E_INVALID_ARG, "distributed ntt: need 2^log_n >= ranks^2");
+    B2_REQUIRE(chunk < (1ull << log_g), B2G16_E_INVALID_ARG, "distributed ntt: chunk index");
+    NttDomain* d = ntt_domain(c, log_n);
+    const int G = 1 << log_g;
+    const uint64_t cols = (1ull << log_n) >> (2 * log_g);
+    Fr wg = host_root_of_unity(log_g);
+    if (inverse) wg = wg.inv();
+    CrossRoots roots;
+    roots.w[0] = Fr::one();
+    for (int i = 1; i < 4; ++i) roots.w[i] = roots.w[i - 1] * wg;
+    // inverse: the local inverse transform already scaled by 1/M; plain needs 1/G more, the coset
+    // variant's g^-e table carries 1/N, so it needs M to end at 1/N overall
+    Fr scale = inverse ? (coset ? host_fr_u64(1ull << (log_n - log_g)) : host_fr_u64((uint64_t)G).inv()) : Fr::one();
+    const Fr* tlo = inverse ? d->tlo_i : d->tlo_f; const Fr* thi = inverse ? d->thi_i : d->thi_f;
+    const int grid = grid_for(cols, 128, 148 * 8);
+#define B2_CROSS(LG) ntt_cross_kernel<LG><<<grid, 128, 0, c->stream>>>(d_in, d_out, cols, chunk * cols, tlo, thi, d->plan.lo_bits, roots, scale, inverse ? 1 : 0, inverse ? 1 : 0, d_bad)
+    if (log_g == 1) B2_CROSS(1); else if (log_g == 2) B2_CROSS(2); else B2_CROSS(3);
+#undef B2_CROSS
+    c->launches++;
+    B2_CUDA(cudaGetLastError());
+}
+void fr_coset_scale_dev(Ctx* c, Fr* d_data, uint64_t count, int log_n, uint64_t offset, bool inverse, int* d_bad) {
+    B2_REQUIRE(offset + count <= (1ull << log_n), B2G16_E_INVALID_ARG, "coset scale: range outside the domain");
+    NttDomain* d = ntt_domain(c, log_n);
+    fr_coset_scale_kernel<<<grid_for(count, 256), 256, 0, c->stream>>>(d_data, count, offset, inverse ? d->glo_i : d->glo_f, inverse ? d->ghi_i : d->ghi_f, d->plan.lo_bits, d_bad);
+    c->launches++;
+    B2_CUDA(cudaGetLastError());
+}
+void fr_transpose_dev(Ctx* c, const Fr* d_in, Fr* d_out, uint64_t rows, uint64_t cols) {
+    fr_transpose_kernel<<<grid_for(rows * cols, 256), 256, 0, c->stream>>>(d_in, d_out, rows, cols);
+    c->launches++;
+    B2_CUDA(cudaGetLastError());
+}
+
 }  // namespace b2

@@ -81,3 +81,81 @@ def prove_partitions(ctx, pk, assignments, rs, ss, group=None):
     world, rank = dist.get_world_size(group), dist.get_rank(group)
     local = {k: ctx.prove(pk, assignments[k], rs[k], ss[k]) for k in my_partitions(len(assignments), rank, world)}
     return gather_proofs(local, len(assignments), group)
+
+
+# ------------------------------------------------------------------ sharded Fr transform
+# One evaluation-domain transform of size N = 2^log_n over G ranks (replaces a
+# single crypto3-math evaluation_domain<Fr>::fft / inverse_fft call when the vector is spread over
+# several GPUs).  Rank r holds x[r M, (r+1) M), M = N / G.  With n = r M + j and k = k1 + G k2:
+#     X[k1 + G k2] = sum_j w_M^(j k2) [ w_N^(j k1) sum_r w_G^(r k1) x[r M + j] ]
+# forward:  all-to-all (columns -> ranks) | cross step | all-to-all (k1 -> ranks) | local size-M
+#           transform: rank k1 now holds X[k1 + G k2] ("cyclic" order) | for "natural" order one more
+#           all-to-all + a local G x M/G transpose.
+# inverse:  the same steps backwards with inverse roots.
+# `ops` supplies the per-rank device steps (b2g16.lib.Context on a GPU; the CPU tests pass an
+# oracle-backed stand-in), tensors are uint8 [M, 32] canonical scalars on the backend's device.
+def _a2a(t, world, group):
+    """t: uint8 [world, rows, 32]; slice i goes to rank i; returns what every rank sent here."""
+    out = torch.empty_like(t)
+    dist.all_to_all_single(out.view(-1), t.contiguous().view(-1), group=group)
+    return out
+
+
+def ntt_sharded(ops, x_local, log_n, inverse=False, coset=False, order="natural", group=None):
+    """x_local: this rank's block (uint8 tensor [M, 32]).  Forward: natural block in -> spectrum out;
+    inverse: spectrum in -> natural block out.  order: layout of the spectrum side -- "natural"
+    (rank r holds X[r M, (r+1) M)) or "cyclic" (rank r holds X[r + G k2], saving one exchange)."""
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    log_g = world.bit_length() - 1
+    assert (1 << log_g) == world and 1 <= log_g <= 3, "ntt_sharded: 2, 4 or 8 ranks"
+    assert log_n >= 2 * log_g and order in ("natural", "cyclic")
+    M = (1 << log_n) >> log_g
+    cols = M >> log_g
+    assert tuple(x_local.shape) == (M, 32) and x_local.dtype == torch.uint8
+    if not inverse:
+        x = x_local.clone() if coset else x_local
+        if coset:
+            ops.fr_coset_scale(x, log_n, rank * M, inverse=False)                     # x[n] *= g^n
+        m1 = _a2a(x.view(world, cols, 32), world, group)                               # [r][j'] for my column chunk
+        m2 = ops.ntt_cross(m1, log_n, log_g, rank, inverse=False, coset=coset)         # [k1][j']
+        y = _a2a(m2, world, group).view(M, 32)                                         # rank k1: all j, natural
+        ops.ntt_local(y, log_n - log_g, inverse=False)                                 # Y[k2] = X[k1 + G k2]
+        if order == "cyclic":
+            return y
+        z = _a2a(y.view(world, cols, 32), world, group)                                # [k1][u] = X[rank M + u G + k1]
+        return ops.fr_transpose(z.view(world * cols, 32), world, cols)                 # -> [u G + k1]
+    if order == "natural":
+        z = ops.fr_transpose(x_local, cols, world)                                     # [k1][u]
+        y = _a2a(z.view(world, cols, 32), world, group).view(M, 32)                    # rank k1: Y[k2] natural
+    else:
+        y = x_local.clone()
+    ops.ntt_local(y, log_n - log_g, inverse=True)                                      # u_{k1}[j], scaled by 1/M
+    m1 = _a2a(y.view(world, cols, 32), world, group)                                   # [k1][j'] for my column chunk
+    m2 = ops.ntt_cross(m1, log_n, log_g, rank, inverse=True, coset=coset)              # [r][j']
+    x = _a2a(m2, world, group).view(M, 32)                                             # rank r: x[r M + j]
+    if coset:
+        ops.fr_coset_scale(x, log_n, rank * M, inverse=True)                           # x[n] *= n^-1 g^-n (cross left 1/n out)
+    return x
+
+
+class DeviceNttOps:
+    """The per-rank steps of ntt_sharded on the GPU: every call is a kernel of libb2g16 on ctx's stream."""
+
+    def __init__(self, ctx):
+        self.ctx = ctx
+
+    def ntt_local(self, t, log_m, inverse):
+        self.ctx.ntt_device(t.data_ptr(), log_m, inverse=inverse, coset=False)
+
+    def ntt_cross(self, m, log_n, log_g, chunk, inverse, coset):
+        out = torch.empty_like(m)
+        self.ctx.ntt_cross_device(m.data_ptr(), out.data_ptr(), log_n, log_g, chunk, inverse, coset)
+        return out
+
+    def fr_coset_scale(self, t, log_n, offset, inverse):
+        self.ctx.fr_coset_scale_device(t.data_ptr(), t.shape[0], log_n, offset, inverse)
+
+    def fr_transpose(self, t, rows, cols):
+        out = torch.empty_like(t)
+        self.ctx.fr_transpose_device(t.data_ptr(), out.data_ptr(), rows, cols)
+        return out

@@ -266,6 +266,17 @@ class Context:
     def ntt_device(self, d_ptr, log_n, inverse=False, coset=False):
         self._chk(load().b2g16_ntt_device(self.h, C.c_void_p(d_ptr), C.c_uint(log_n), int(inverse), int(coset)))
 
+    # per-rank steps of the transform sharded over several GPUs (dist.ntt_sharded)
+    def ntt_cross_device(self, d_in, d_out, log_n, log_g, chunk, inverse=False, coset=False):
+        self._chk(load().b2g16_ntt_cross_device(self.h, C.c_void_p(d_in), C.c_void_p(d_out), C.c_uint(log_n), C.c_uint(log_g), C.c_uint(chunk),
+                                                int(inverse), int(coset)))
+
+    def fr_coset_scale_device(self, d_ptr, count, log_n, offset, inverse=False):
+        self._chk(load().b2g16_fr_coset_scale_device(self.h, C.c_void_p(d_ptr), C.c_size_t(count), C.c_uint(log_n), C.c_uint64(offset), int(inverse)))
+
+    def fr_transpose_device(self, d_in, d_out, rows, cols):
+        self._chk(load().b2g16_fr_transpose_device(self.h, C.c_void_p(d_in), C.c_void_p(d_out), C.c_size_t(rows), C.c_size_t(cols)))
+
     def h_from_abc(self, a, b, c):
         a, b, c = _u8(a, 32), _u8(b, 32), _u8(c, 32)
         m = a.shape[0]

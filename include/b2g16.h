@@ -82,6 +82,17 @@ int b2g16_g2_sum(b2g16_ctx*, const uint8_t* pts192, size_t n, uint8_t out192[192
 int b2g16_ntt(b2g16_ctx*, uint8_t* fr32_inout, unsigned log_n, int inverse, int coset);
 /* device-resident variant: d_data holds 2^log_n canonical 32-byte scalars */
 int b2g16_ntt_device(b2g16_ctx*, uint8_t* d_fr32_inout, unsigned log_n, int inverse, int coset);
+/* One transform of size 2^log_n sharded over G = 2^log_g GPUs (rank r holds elements
+ * [r M, (r+1) M), M = 2^log_n / G).  The exchanges are all-to-alls done by the host over NCCL
+ * (python/b2g16/dist.py::ntt_sharded shows the sequence); these are the device steps in between:
+ *   cross:     per column of a G x (M/G) row-major matrix, a G-point transform and the twiddle
+ *              w_N^(j k1), j = chunk * M/G + column  (forward: transform then twiddle; inverse: twiddle,
+ *              inverse transform, 1/G).  With `coset` the inverse leaves the factor to the g^-e table.
+ *   coset_scale: x[i] *= g^(offset+i)  (inverse: n^-1 g^-(offset+i)) for the rank's block of the domain.
+ *   transpose: rows x cols -> cols x rows of 32-byte elements (cyclic <-> block order of a rank's spectrum). */
+int b2g16_ntt_cross_device(b2g16_ctx*, const uint8_t* d_in, uint8_t* d_out, unsigned log_n, unsigned log_g, unsigned chunk, int inverse, int coset);
+int b2g16_fr_coset_scale_device(b2g16_ctx*, uint8_t* d_fr32_inout, size_t count, unsigned log_n, uint64_t offset, int inverse);
+int b2g16_fr_transpose_device(b2g16_ctx*, const uint8_t* d_in, uint8_t* d_out, size_t rows, size_t cols);
 
 /* ---- r1cs_to_qap witness map tail: a,b,c evaluations on the domain ->
  *      coefficients of H = (A*B - C)/Z  (m values, h[m-1] = 0). */
