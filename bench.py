@@ -41,8 +41,9 @@ METRIC = "groth16_c2_partition_prove_s"
 
 
 def n_in_of(workload):
+    from b2g16 import shapes
     log_m, ch, _ = WORKLOADS[workload]
-    return 1 if ch == 0 else 3 + 18 * ch
+    return 1 if ch == 0 else shapes.porep_public_inputs(ch)
 
 
 def peaks():

@@ -198,12 +198,44 @@ template <class CurveType> struct r1cs_gg_ppzksnark {
         g1_value g_A, g_C;
         g2_value g_B;
         const std::array<std::uint8_t, 192>& bytes() const { return compressed; }
+        // multi_proof write / new_from_reader (F/api/seal.hpp:304-308, 382-383): 192 bytes per proof
+        void write(std::uint8_t* out) const { std::memcpy(out, compressed.data(), 192); }
+        static proof_type read(const std::uint8_t* in) {                // validates encoding, curve, subgroup
+            proof_type p;
+            std::memcpy(p.compressed.data(), in, 192);
+            int rc = b2g16_proof_decode(in, p.g_A.data.data(), p.g_B.data.data(), p.g_C.data.data());
+            if (rc != B2G16_OK) throw b2g16::error(rc, "proof: malformed 192-byte encoding");
+            return p;
+        }
     };
     struct verification_key_type {
         g1_value alpha_g1; g2_value beta_g2, gamma_g2, delta_g2; std::vector<g1_value> gamma_ABC_g1;
     };
     typedef verification_key_type verifying_key_type;            // both spellings occur (scheme_params.hpp:44, multi_proof.hpp:43)
-    typedef verification_key_type processed_verification_key_type;
+    // the `pvk` kept next to the mapped proving key (mapped_scheme_params.hpp:61): alpha/beta Miller value
+    // cached on the host, IC bases resident on the device
+    class processed_verification_key_type {
+        b2g16_pvk* h_ = nullptr;
+        std::size_t n_in_ = 0;
+    public:
+        processed_verification_key_type() {}
+        explicit processed_verification_key_type(const verification_key_type& vk) : n_in_(vk.gamma_ABC_g1.size() - 1) {
+            std::vector<std::uint8_t> b(672 + 96 * vk.gamma_ABC_g1.size());
+            std::memcpy(b.data(), vk.alpha_g1.data.data(), 96); std::memcpy(b.data() + 96, vk.beta_g2.data.data(), 192);
+            std::memcpy(b.data() + 288, vk.gamma_g2.data.data(), 192); std::memcpy(b.data() + 480, vk.delta_g2.data.data(), 192);
+            std::memcpy(b.data() + 672, vk.gamma_ABC_g1.data(), 96 * vk.gamma_ABC_g1.size());
+            b2g16::context& c = b2g16::context::instance();
+            c.check(b2g16_vk_prepare(c.get(), b.data(), vk.gamma_ABC_g1.size(), &h_));
+        }
+        processed_verification_key_type(processed_verification_key_type&& o) noexcept : h_(o.h_), n_in_(o.n_in_) { o.h_ = nullptr; }
+        processed_verification_key_type& operator=(processed_verification_key_type&& o) noexcept { reset(); h_ = o.h_; n_in_ = o.n_in_; o.h_ = nullptr; return *this; }
+        processed_verification_key_type(const processed_verification_key_type&) = delete;
+        processed_verification_key_type& operator=(const processed_verification_key_type&) = delete;
+        ~processed_verification_key_type() { reset(); }
+        void reset() { if (h_) { b2g16_pvk_free(b2g16::context::instance().get(), h_); h_ = nullptr; } }
+        const b2g16_pvk* handle() const { return h_; }
+        std::size_t num_inputs() const { return n_in_; }
+    };
 
     // Device-resident proving key (scheme_params.hpp:38-67 layout: vk, h, l, a, b_g1, b_g2), dense.
     class proving_key_type {
@@ -289,6 +321,39 @@ typename Scheme::proof_type prove(const typename Scheme::proving_key_type& pk, c
     typename Scheme::fr_value r, s;
     for (auto* v : {&r, &s}) { for (auto& b : v->data) b = (std::uint8_t)rd(); v->data[31] &= 0x3f; }   // < 2^254 < r
     return prove<Scheme>(pk, primary, auxiliary, r, s);
+}
+
+// verify<Scheme>(pvk, primary_input, proof): the check behind compound_proof::verify
+// (S/core/proof/compound_proof.hpp:97-102) that seal_commit_phase2 runs on its own output
+// (F/api/seal.hpp:310-313).  A malformed proof is `false`, not an exception.
+template <class Scheme>
+bool verify(const typename Scheme::processed_verification_key_type& pvk, const typename Scheme::primary_input_type& primary,
+            const typename Scheme::proof_type& proof) {
+    b2g16::context& c = b2g16::context::instance();
+    int ok = 0;
+    c.check(b2g16_verify(c.get(), pvk.handle(), reinterpret_cast<const std::uint8_t*>(primary.data()), primary.size(), proof.compressed.data(), &ok));
+    return ok != 0;
+}
+template <class Scheme>
+bool verify(const typename Scheme::verification_key_type& vk, const typename Scheme::primary_input_type& primary, const typename Scheme::proof_type& proof) {
+    typename Scheme::processed_verification_key_type pvk(vk);
+    return verify<Scheme>(pvk, primary, proof);
+}
+// all partitions of a multi_proof in one product (verify_batch_seal, F/api/seal.hpp:409-485)
+template <class Scheme>
+bool verify_batch(const typename Scheme::processed_verification_key_type& pvk, const std::vector<typename Scheme::primary_input_type>& primaries,
+                  const std::vector<typename Scheme::proof_type>& proofs) {
+    if (primaries.size() != proofs.size()) throw b2g16::error(B2G16_E_INVALID_ARG, "verify_batch: one input vector per proof");
+    std::vector<std::uint8_t> in, pr;
+    for (const auto& v : primaries) {
+        if (v.size() != pvk.num_inputs()) throw b2g16::error(B2G16_E_INVALID_ARG, "verify_batch: public input count differs from the key");
+        in.insert(in.end(), reinterpret_cast<const std::uint8_t*>(v.data()), reinterpret_cast<const std::uint8_t*>(v.data()) + 32 * v.size());
+    }
+    for (const auto& p : proofs) pr.insert(pr.end(), p.compressed.begin(), p.compressed.end());
+    b2g16::context& c = b2g16::context::instance();
+    int ok = 0;
+    c.check(b2g16_verify_batch(c.get(), pvk.handle(), in.data(), pvk.num_inputs(), pr.data(), proofs.size(), nullptr, &ok));
+    return ok != 0;
 }
 
 }  // namespace snark

@@ -80,6 +80,23 @@ int main(int argc, char** argv) {
         expect(proof.g_A == load<g1>("proof_A")[0] && proof.g_B == load<g2>("proof_B")[0] && proof.g_C == load<g1>("proof_C")[0], "prove: g_A, g_B, g_C");
         auto p2 = zk::snark::prove<scheme>(kp.first, primary, aux);                          // random r, s: valid, different bytes
         expect(memcmp(p2.bytes().data(), want.data(), 192) != 0, "prove with drawn r, s differs");
+        // the seal_commit_phase2 tail (F/api/seal.hpp:304-313): write the multi-proof bytes, read them back, verify
+        scheme::processed_verification_key_type pvk(kp.second);
+        expect(zk::snark::verify<scheme>(pvk, primary, proof), "verify: oracle-identical proof accepted");
+        expect(zk::snark::verify<scheme>(pvk, primary, p2), "verify: proof with drawn r, s accepted");
+        expect(zk::snark::verify<scheme>(kp.second, primary, proof), "verify: from the plain verification key");
+        std::uint8_t buf[384];
+        proof.write(buf); p2.write(buf + 192);
+        auto q = scheme::proof_type::read(buf);
+        expect(q.g_A == proof.g_A && q.g_B == proof.g_B && q.g_C == proof.g_C, "proof read back: same points");
+        expect(zk::snark::verify_batch<scheme>(pvk, {primary, primary}, {q, scheme::proof_type::read(buf + 192)}), "verify_batch: two partitions");
+        auto bad_in = primary; bad_in[0].data[0] ^= 1;
+        expect(!zk::snark::verify<scheme>(pvk, bad_in, proof), "verify: perturbed public input rejected");
+        expect(!zk::snark::verify_batch<scheme>(pvk, {primary, bad_in}, {proof, p2}), "verify_batch: one bad input sinks the batch");
+        buf[0] &= 0x7f;
+        bool threw = false;
+        try { scheme::proof_type::read(buf); } catch (const b2g16::error&) { threw = true; }
+        expect(threw, "proof read: malformed encoding throws");
     }
     printf("%s\n", fails ? "SHIM TEST FAILED" : "shim test passed");
     return fails ? 1 : 0;
