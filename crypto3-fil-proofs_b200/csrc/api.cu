@@ -230,6 +230,54 @@ int b2g16_ntt_cross_device(b2g16_ctx* h, const uint8_t* d_in, uint8_t* d_out, un
         bad.check("scalars");
     });
 }
+// ---- peer memory: buffers other ranks' kernels may load from / store to over NVLink (CUDA IPC)
+int b2g16_peer_alloc(b2g16_ctx* h, size_t bytes, uint8_t** d_ptr, uint8_t handle_out[64]) {
+    Ctx* c = reinterpret_cast<Ctx*>(h);
+    if (!c || !d_ptr || !handle_out || bytes == 0) return B2G16_E_INVALID_ARG;
+    static_assert(sizeof(cudaIpcMemHandle_t) == 64, "IPC handle size");
+    return guard(c, [&] {
+        void* p = nullptr;
+        B2_CUDA(cudaMalloc(&p, bytes));                      // a whole allocation: IPC handles name allocations, not sub-ranges
+        cudaIpcMemHandle_t hd;
+        cudaError_t e = cudaIpcGetMemHandle(&hd, p);
+        if (e != cudaSuccess) { cudaFree(p); B2_CUDA(e); }
+        memcpy(handle_out, &hd, 64);
+        *d_ptr = (uint8_t*)p;
+    });
+}
+int b2g16_peer_open(b2g16_ctx* h, const uint8_t handle[64], uint8_t** d_peer_ptr) {
+    Ctx* c = reinterpret_cast<Ctx*>(h);
+    if (!c || !handle || !d_peer_ptr) return B2G16_E_INVALID_ARG;
+    return guard(c, [&] {
+        cudaIpcMemHandle_t hd; memcpy(&hd, handle, 64);
+        void* p = nullptr;
+        B2_CUDA(cudaIpcOpenMemHandle(&p, hd, cudaIpcMemLazyEnablePeerAccess));
+        *d_peer_ptr = (uint8_t*)p;
+    });
+}
+int b2g16_peer_close(b2g16_ctx* h, uint8_t* d_peer_ptr) {
+    Ctx* c = reinterpret_cast<Ctx*>(h);
+    if (!c || !d_peer_ptr) return B2G16_E_INVALID_ARG;
+    return guard(c, [&] { B2_CUDA(cudaStreamSynchronize(c->stream)); B2_CUDA(cudaIpcCloseMemHandle(d_peer_ptr)); });
+}
+int b2g16_peer_free(b2g16_ctx* h, uint8_t* d_ptr) {
+    Ctx* c = reinterpret_cast<Ctx*>(h);
+    if (!c || !d_ptr) return B2G16_E_INVALID_ARG;
+    return guard(c, [&] { B2_CUDA(cudaStreamSynchronize(c->stream)); B2_CUDA(cudaFree(d_ptr)); });
+}
+// cross step fused with both of its exchanges: loads straight from every rank's block, stores straight
+// into every rank's output buffer.  The caller brackets it with barriers (inputs ready / outputs landed).
+int b2g16_ntt_cross_p2p_device(b2g16_ctx* h, const uint8_t* const* d_in_peers, uint8_t* const* d_out_peers, unsigned log_n, unsigned log_g,
+                               unsigned rank, int inverse, int coset) {
+    Ctx* c = reinterpret_cast<Ctx*>(h);
+    if (!c || !d_in_peers || !d_out_peers) return B2G16_E_INVALID_ARG;
+    return guard(c, [&] {
+        DevFlag bad(c);
+        ntt_cross_p2p_dev(c, reinterpret_cast<const Fr* const*>(d_in_peers), reinterpret_cast<Fr* const*>(d_out_peers), (int)log_n, (int)log_g, rank,
+                          inverse != 0, coset != 0, bad.ptr());
+        bad.check("scalars");
+    });
+}
 int b2g16_fr_coset_scale_device(b2g16_ctx* h, uint8_t* d_fr32_inout, size_t count, unsigned log_n, uint64_t offset, int inverse) {
     Ctx* c = reinterpret_cast<Ctx*>(h);
     if (!c || (count && !d_fr32_inout) || log_n > 30) return B2G16_E_INVALID_ARG;

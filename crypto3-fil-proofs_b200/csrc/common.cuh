@@ -93,6 +93,7 @@ void ntt_natural(Ctx* c, Fr* d_data, int log_n, bool inverse, bool coset);
 bool ntt_needs_tmp(int log_n);
 // building blocks of the transform sharded over 2^log_g ranks (see ntt.cu "distributed transform")
 void ntt_cross_dev(Ctx* c, const Fr* d_in, Fr* d_out, int log_n, int log_g, uint64_t chunk, bool inverse, bool coset, int* d_bad);
+void ntt_cross_p2p_dev(Ctx* c, const Fr* const* peers_in, Fr* const* peers_out, int log_n, int log_g, uint64_t rank, bool inverse, bool coset, int* d_bad);
 void fr_coset_scale_dev(Ctx* c, Fr* d_data, uint64_t count, int log_n, uint64_t offset, bool inverse, int* d_bad);
 void fr_transpose_dev(Ctx* c, const Fr* d_in, Fr* d_out, uint64_t rows, uint64_t cols);
 Fr host_root_of_unity(int log_n);

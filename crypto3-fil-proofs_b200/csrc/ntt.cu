@@ -158,16 +158,21 @@ void h_from_abc_dev(Ctx* c, Fr* d_a, Fr* d_b, Fr* d_c, int log_m, uint32_t* d_h_
 // the inverse G-point transform, times `scale`.  Data stays in canonical form throughout
 // (the transform is linear and every constant is in Montgomery form; ntt_plan.cuh).
 struct CrossRoots { Fr w[4]; };       // w_G^i (forward or inverse), i < G/2, G <= 8
+// Row r of the input / row k of the output, each `cols` elements.  Local form: rows of one G x cols
+// matrix.  Peer form: in[r] points into rank r's block and out[k] into rank k's buffer, both mapped
+// into this process with CUDA IPC, so the two exchanges around the cross step become NVLink loads and
+// stores issued by the kernel itself (compute and transfer overlap thread by thread; no staging pass).
+struct CrossPtrs { const Fr* in[8]; Fr* out[8]; };
 
 template <int LOG_G> __global__ void __launch_bounds__(128)
-ntt_cross_kernel(const Fr* __restrict__ in, Fr* __restrict__ out, uint64_t cols, uint64_t col0, const Fr* __restrict__ tlo,
+ntt_cross_kernel(const CrossPtrs ptrs, uint64_t cols, uint64_t col0, const Fr* __restrict__ tlo,
                  const Fr* __restrict__ thi, int lo_bits, CrossRoots roots, Fr scale, int inverse, int use_scale, int* bad) {
     constexpr int G = 1 << LOG_G;
     for (uint64_t jj = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; jj < cols; jj += (uint64_t)gridDim.x * blockDim.x) {
         Fr v[G];
 #pragma unroll
         for (int r = 0; r < G; ++r) {
-            v[r] = fr_load(in + (uint64_t)r * cols + jj);
+            v[r] = fr_load(ptrs.in[r] + jj);
             if (bad && Fr::geq_p(v[r].v)) atomicOr(bad, 1);
         }
         const uint64_t j = col0 + jj;                               // global column: exponent of the twiddle base
@@ -210,7 +215,7 @@ ntt_cross_kernel(const Fr* __restrict__ in, Fr* __restrict__ out, uint64_t cols,
             int src = 0;
 #pragma unroll
             for (int bit = 0; bit < LOG_G; ++bit) src |= ((k >> bit) & 1) << (LOG_G - 1 - bit);
-            fr_store(out + (uint64_t)k * cols + jj, v[src]);
+            fr_store(ptrs.out[k] + jj, v[src]);
         }
     }
 }
@@ -237,7 +242,27 @@ __global__ void __launch_bounds__(256) fr_transpose_kernel(const Fr* __restrict_
     }
 }
 
+static void ntt_cross_launch(Ctx* c, const CrossPtrs& ptrs, int log_n, int log_g, uint64_t chunk, bool inverse, bool coset, int* d_bad);
+
 void ntt_cross_dev(Ctx* c, const Fr* d_in, Fr* d_out, int log_n, int log_g, uint64_t chunk, bool inverse, bool coset, int* d_bad) {
+    B2_REQUIRE(log_g >= 1 && log_g <= 3 && log_n >= 2 * log_g && log_n <= 30, B2G16_E_INVALID_ARG, "distributed ntt: 2, 4 or 8 ranks, 2^log_n >= ranks^2");
+    const uint64_t cols = (1ull << log_n) >> (2 * log_g);
+    CrossPtrs ptrs{};
+    for (int r = 0; r < (1 << log_g); ++r) { ptrs.in[r] = d_in + (uint64_t)r * cols; ptrs.out[r] = d_out + (uint64_t)r * cols; }
+    ntt_cross_launch(c, ptrs, log_n, log_g, chunk, inverse, coset, d_bad);
+}
+// peers_in[r] / peers_out[k]: base of rank r's (k's) M-element buffer as mapped in this process
+void ntt_cross_p2p_dev(Ctx* c, const Fr* const* peers_in, Fr* const* peers_out, int log_n, int log_g, uint64_t rank, bool inverse, bool coset, int* d_bad) {
+    B2_REQUIRE(log_g >= 1 && log_g <= 3 && log_n >= 2 * log_g && log_n <= 30, B2G16_E_INVALID_ARG, "distributed ntt: 2, 4 or 8 ranks, 2^log_n >= ranks^2");
+    const uint64_t cols = (1ull << log_n) >> (2 * log_g);
+    CrossPtrs ptrs{};
+    for (int r = 0; r < (1 << log_g); ++r) {
+        B2_REQUIRE(peers_in[r] && peers_out[r], B2G16_E_INVALID_ARG, "distributed ntt: missing peer buffer");
+        ptrs.in[r] = peers_in[r] + rank * cols; ptrs.out[r] = peers_out[r] + rank * cols;
+    }
+    ntt_cross_launch(c, ptrs, log_n, log_g, rank, inverse, coset, d_bad);
+}
+static void ntt_cross_launch(Ctx* c, const CrossPtrs& ptrs, int log_n, int log_g, uint64_t chunk, bool inverse, bool coset, int* d_bad) {
     B2_REQUIRE(log_g >= 1 && log_g <= 3, B2G16_E_INVALID_ARG, "distributed ntt: 2, 4 or 8 ranks");
     B2_REQUIRE(log_n >= 2 * log_g && log_n <= 30, B2G16_E_INVALID_ARG, "distributed ntt: need 2^log_n >= ranks^2");
     B2_REQUIRE(chunk < (1ull << log_g), B2G16_E_INVALID_ARG, "distributed ntt: chunk index");
@@ -254,7 +279,7 @@ void ntt_cross_dev(Ctx* c, const Fr* d_in, Fr* d_out, int log_n, int log_g, uint
     Fr scale = inverse ? (coset ? host_fr_u64(1ull << (log_n - log_g)) : host_fr_u64((uint64_t)G).inv()) : Fr::one();
     const Fr* tlo = inverse ? d->tlo_i : d->tlo_f; const Fr* thi = inverse ? d->thi_i : d->thi_f;
     const int grid = grid_for(cols, 128, 148 * 8);
-#define B2_CROSS(LG) ntt_cross_kernel<LG><<<grid, 128, 0, c->stream>>>(d_in, d_out, cols, chunk * cols, tlo, thi, d->plan.lo_bits, roots, scale, inverse ? 1 : 0, inverse ? 1 : 0, d_bad)
+#define B2_CROSS(LG) ntt_cross_kernel<LG><<<grid, 128, 0, c->stream>>>(ptrs, cols, chunk * cols, tlo, thi, d->plan.lo_bits, roots, scale, inverse ? 1 : 0, inverse ? 1 : 0, d_bad)
     if (log_g == 1) B2_CROSS(1); else if (log_g == 2) B2_CROSS(2); else B2_CROSS(3);
 #undef B2_CROSS
     c->launches++;

@@ -159,3 +159,80 @@ class DeviceNttOps:
         out = torch.empty_like(t)
         self.ctx.fr_transpose_device(t.data_ptr(), out.data_ptr(), rows, cols)
         return out
+
+
+class _RawDeviceBytes:
+    """torch.as_tensor adaptor for a raw device pointer owned by the library"""
+
+    def __init__(self, ptr, nbytes):
+        self.__cuda_array_interface__ = {"shape": (nbytes,), "typestr": "|u1", "data": (ptr, False), "version": 2}
+
+
+class PeerNtt:
+    """The sharded transform with the cross step and both of its exchanges fused into one kernel over NVLink
+    peer memory (b2g16_ntt_cross_p2p_device): every rank owns two IPC-exported buffers, `x` (its natural
+    block, M scalars) and `y` (its cyclic spectrum block); the kernel loads its column chunk from all x's
+    and stores row k1 into rank k1's y (inverse: the other way round).  What is left of the collective is
+    two barriers.  NCCL is used only for the handle exchange at construction and the barriers.
+        forward : x (natural block) -> y = X[rank + G k2]      inverse : y -> x
+    x and y are uint8 [M, 32] torch views of the library's buffers; fill x (or y) in place."""
+
+    def __init__(self, ctx, log_n, group=None):
+        self.ctx, self.log_n, self.group = ctx, log_n, group
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.log_g = self.world.bit_length() - 1
+        assert (1 << self.log_g) == self.world and 1 <= self.log_g <= 3 and log_n >= 2 * self.log_g
+        self.M = (1 << log_n) >> self.log_g
+        nbytes = self.M * 32
+        self._own, handles = [], []
+        for _ in range(2):
+            ptr, h = ctx.peer_alloc(nbytes)
+            self._own.append(ptr)
+            handles.append(h)
+        allh = [None] * self.world
+        dist.all_gather_object(allh, handles, group=group)
+        self._opened = []
+        self.x_ptrs, self.y_ptrs = [], []
+        for r in range(self.world):
+            for which, lst in ((0, self.x_ptrs), (1, self.y_ptrs)):
+                if r == self.rank:
+                    lst.append(self._own[which])
+                else:
+                    p = ctx.peer_open(allh[r][which])
+                    self._opened.append(p)
+                    lst.append(p)
+        dev = torch.device("cuda", torch.cuda.current_device())
+        self.x = torch.as_tensor(_RawDeviceBytes(self._own[0], nbytes), device=dev).view(self.M, 32)
+        self.y = torch.as_tensor(_RawDeviceBytes(self._own[1], nbytes), device=dev).view(self.M, 32)
+
+    def _barrier(self):
+        torch.cuda.current_stream().synchronize()
+        dist.barrier(group=self.group)
+
+    def forward(self, coset=False):
+        if coset:
+            self.ctx.fr_coset_scale_device(self.x.data_ptr(), self.M, self.log_n, self.rank * self.M, False)
+        self._barrier()                                                  # every x written, every y free
+        self.ctx.ntt_cross_p2p_device(self.x_ptrs, self.y_ptrs, self.log_n, self.log_g, self.rank, False, coset)
+        self._barrier()                                                  # every store into my y has landed
+        self.ctx.ntt_device(self.y.data_ptr(), self.log_n - self.log_g, inverse=False, coset=False)
+        return self.y
+
+    def inverse(self, coset=False):
+        self.ctx.ntt_device(self.y.data_ptr(), self.log_n - self.log_g, inverse=True, coset=False)
+        self._barrier()
+        self.ctx.ntt_cross_p2p_device(self.y_ptrs, self.x_ptrs, self.log_n, self.log_g, self.rank, True, coset)
+        self._barrier()
+        if coset:
+            self.ctx.fr_coset_scale_device(self.x.data_ptr(), self.M, self.log_n, self.rank * self.M, True)
+        return self.x
+
+    def close(self):
+        self._barrier()
+        for p in self._opened:
+            self.ctx.peer_close(p)
+        self._opened = []
+        self._barrier()
+        for p in self._own:
+            self.ctx.peer_free(p)
+        self._own = []

@@ -277,6 +277,29 @@ class Context:
     def fr_transpose_device(self, d_in, d_out, rows, cols):
         self._chk(load().b2g16_fr_transpose_device(self.h, C.c_void_p(d_in), C.c_void_p(d_out), C.c_size_t(rows), C.c_size_t(cols)))
 
+    # peer memory (CUDA IPC) and the cross step fused with its exchanges
+    def peer_alloc(self, nbytes):
+        """-> (device pointer, 64-byte IPC handle) of a fresh whole allocation"""
+        ptr, handle = C.c_void_p(), np.zeros(64, dtype=np.uint8)
+        self._chk(load().b2g16_peer_alloc(self.h, C.c_size_t(nbytes), C.byref(ptr), _p(handle)))
+        return int(ptr.value), handle.tobytes()
+
+    def peer_open(self, handle):
+        ptr = C.c_void_p()
+        self._chk(load().b2g16_peer_open(self.h, _p(np.frombuffer(handle, dtype=np.uint8).copy()), C.byref(ptr)))
+        return int(ptr.value)
+
+    def peer_close(self, ptr):
+        self._chk(load().b2g16_peer_close(self.h, C.c_void_p(ptr)))
+
+    def peer_free(self, ptr):
+        self._chk(load().b2g16_peer_free(self.h, C.c_void_p(ptr)))
+
+    def ntt_cross_p2p_device(self, in_ptrs, out_ptrs, log_n, log_g, rank, inverse=False, coset=False):
+        n = len(in_ptrs)
+        a, b = (C.c_void_p * n)(*in_ptrs), (C.c_void_p * n)(*out_ptrs)
+        self._chk(load().b2g16_ntt_cross_p2p_device(self.h, a, b, C.c_uint(log_n), C.c_uint(log_g), C.c_uint(rank), int(inverse), int(coset)))
+
     def h_from_abc(self, a, b, c):
         a, b, c = _u8(a, 32), _u8(b, 32), _u8(c, 32)
         m = a.shape[0]

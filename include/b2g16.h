@@ -91,6 +91,18 @@ int b2g16_ntt_device(b2g16_ctx*, uint8_t* d_fr32_inout, unsigned log_n, int inve
  *   coset_scale: x[i] *= g^(offset+i)  (inverse: n^-1 g^-(offset+i)) for the rank's block of the domain.
  *   transpose: rows x cols -> cols x rows of 32-byte elements (cyclic <-> block order of a rank's spectrum). */
 int b2g16_ntt_cross_device(b2g16_ctx*, const uint8_t* d_in, uint8_t* d_out, unsigned log_n, unsigned log_g, unsigned chunk, int inverse, int coset);
+/* The cross step fused with both exchanges around it: d_in_peers[r] / d_out_peers[k] are the bases of rank
+ * r's input block and rank k's output buffer (M scalars each) as mapped into this process; the kernel loads
+ * its column chunk from every peer and stores row k straight into peer k over NVLink.  The caller orders it
+ * with a barrier before (inputs written, outputs free) and after (stores landed).  Peer buffers:
+ * b2g16_peer_alloc (cudaMalloc + IPC handle, 64 bytes, to be exchanged by the host), b2g16_peer_open /
+ * _close on the other ranks, b2g16_peer_free by the owner. */
+int b2g16_peer_alloc(b2g16_ctx*, size_t bytes, uint8_t** d_ptr, uint8_t handle_out[64]);
+int b2g16_peer_open(b2g16_ctx*, const uint8_t handle[64], uint8_t** d_peer_ptr);
+int b2g16_peer_close(b2g16_ctx*, uint8_t* d_peer_ptr);
+int b2g16_peer_free(b2g16_ctx*, uint8_t* d_ptr);
+int b2g16_ntt_cross_p2p_device(b2g16_ctx*, const uint8_t* const* d_in_peers, uint8_t* const* d_out_peers, unsigned log_n, unsigned log_g,
+                               unsigned rank, int inverse, int coset);
 int b2g16_fr_coset_scale_device(b2g16_ctx*, uint8_t* d_fr32_inout, size_t count, unsigned log_n, uint64_t offset, int inverse);
 int b2g16_fr_transpose_device(b2g16_ctx*, const uint8_t* d_in, uint8_t* d_out, size_t rows, size_t cols);
 

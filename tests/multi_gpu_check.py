@@ -52,6 +52,21 @@ def main():
         assert torch.equal(spec, full[rank::world].contiguous()), ("ntt cyclic", log_n, rank)
         assert torch.equal(bd.ntt_sharded(ops, spec, log_n, inverse=True, order="cyclic"), mine), ("ntt cyclic inverse", log_n, rank)
         checks += 2
+    # ---- the same transform with the cross step fused with its exchanges over NVLink peer memory
+    for log_n in sorted({2 * log_g, 12, 21}):
+        n, M = 1 << log_n, (1 << log_n) // world
+        x = torch.from_numpy(codec.random_fr(n, np.random.Generator(np.random.PCG64(90 + log_n)))).to(dev)
+        pn = bd.PeerNtt(ctx, log_n)
+        for coset in (False, True):
+            full = x.clone()
+            ctx.ntt_device(full.data_ptr(), log_n, inverse=False, coset=coset)
+            pn.x.copy_(x[rank * M:(rank + 1) * M])
+            spec = pn.forward(coset=coset)
+            assert torch.equal(spec, full[rank::world].contiguous()), ("p2p ntt forward", log_n, coset, rank)
+            back = pn.inverse(coset=coset)                                # y still holds the spectrum
+            assert torch.equal(back, x[rank * M:(rank + 1) * M]), ("p2p ntt inverse", log_n, coset, rank)
+            checks += 2
+        pn.close()
     # ---- multiexp by point range
     n = 50000 + 7
     rng = np.random.Generator(np.random.PCG64(5))
