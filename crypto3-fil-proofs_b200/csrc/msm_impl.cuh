@@ -494,9 +494,17 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
 
     // G2 at 16-bit windows: the one-thread-per-bucket kernel is faster (measured 86 vs 99 ms at 2^22)
     const bool chunked = ctx->acc_variant >= 100 && !(sizeof(F) > 48 && c <= 16);
-    constexpr int CH_THREADS = sizeof(F) > 48 ? 64 : 128;
-    const int ch_minb = !chunked ? 0 : (sizeof(F) > 48 ? 4 : ctx->acc_variant - 100);   // G2: 64-thread CTAs at the 255-register cap, 4 per SM
-    const uint32_t n_chunks = chunked ? (uint32_t)(148 * ch_minb * CH_THREADS) : 0;
+    // chunked-accumulate launch shape (threads per CTA, CTAs per SM).  G1 at 194 registers per thread: 2 x 160
+    // threads = 10 warps per SM is the most that fits the register file without spilling (variant 105);
+    // 101..104 = 128-thread CTAs, 1..4 per SM; 106 = 3 x 96.  G2: 64-thread CTAs at the 255-register cap, 4 per SM.
+    int ch_threads = 0, ch_minb = 0;
+    if (chunked) {
+        if (sizeof(F) > 48) { ch_threads = 64; ch_minb = 4; }
+        else if (ctx->acc_variant == 105) { ch_threads = 160; ch_minb = 2; }
+        else if (ctx->acc_variant == 106) { ch_threads = 96; ch_minb = 3; }
+        else { ch_threads = 128; ch_minb = ctx->acc_variant - 100; }
+    }
+    const uint32_t n_chunks = chunked ? (uint32_t)(148 * ch_minb * ch_threads) : 0;
     DevBuf<uint32_t> hist(nb + 1, st), off(nb + 1, st), cursor(nb + 1, st), seg_off(chunked ? 0 : nb + 1, st), tile_sums((size_t)n_tiles + 1, st), sorted(max_entries, st);
     DevBuf<Xyzz<F>> seg_acc(chunked ? nb : max_segs, st), pieces(2 * (size_t)n_chunks, st);
     DevBuf<uint32_t> piece_bucket(2 * (size_t)n_chunks, st);
@@ -524,13 +532,16 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
         B2_CUDA(cudaMemsetAsync(seg_acc.get(), 0, nb * sizeof(Xyzz<F>), st));            // empty bucket = identity (ZZ = 0)
         Xyzz<F>* head = pieces.get(); Xyzz<F>* tail = pieces.get() + n_chunks;
         uint32_t* hb = piece_bucket.get(); uint32_t* tb = piece_bucket.get() + n_chunks;
-#define B2_CH(MINB) msm_accumulate_chunked_kernel<F, CH_THREADS, MINB><<<148 * MINB, CH_THREADS, 0, st>>>(d_bases, sorted.get(), off.get(), (uint32_t)nb, seg_acc.get(), head, tail, hb, tb)
-        switch (ch_minb) {
-            case 1: B2_CH(1); break;
-            case 2: B2_CH(2); break;
-            case 3: B2_CH(3); break;
-            case 4: B2_CH(4); break;
-            default: B2_REQUIRE(false, B2G16_E_INVALID_ARG, "msm: chunked accumulate variant must be 101..104");
+#define B2_CH(THREADS, MINB) msm_accumulate_chunked_kernel<F, THREADS, MINB><<<148 * MINB, THREADS, 0, st>>>(d_bases, sorted.get(), off.get(), (uint32_t)nb, seg_acc.get(), head, tail, hb, tb)
+        if (sizeof(F) > 48) B2_CH(64, 4);
+        else switch (ctx->acc_variant) {
+            case 101: B2_CH(128, 1); break;
+            case 102: B2_CH(128, 2); break;
+            case 103: B2_CH(128, 3); break;
+            case 104: B2_CH(128, 4); break;
+            case 105: B2_CH(160, 2); break;
+            case 106: B2_CH(96, 3); break;
+            default: B2_REQUIRE(false, B2G16_E_INVALID_ARG, "msm: chunked accumulate variant must be 101..106");
         }
 #undef B2_CH
         msm_fix_pieces_kernel<F><<<grid_for((size_t)n_chunks * 32, 128, 148 * 16), 128, 0, st>>>(seg_acc.get(), head, tail, hb, tb, n_chunks);
