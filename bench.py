@@ -307,6 +307,23 @@ def run_b200(args):
         "gpu_launches": int(launches), "roofline": roofline, "clocks": clocks, "setup_s": t_setup,
     }
 
+    if world > 1:
+        # latency mode: the same proof with its five multiexps range-sharded over all ranks;
+        # rank 0's witness everywhere (the other ranks' own witnesses belong to the weak-scaling figure above)
+        from b2g16 import dist as bd
+        dist.broadcast(dz, src=0)
+        strong = []
+        p_ref = bd.prove_sharded(ctx, pk, dz.data_ptr(), r, sr)
+        for _ in range(3):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier(); e0.record(); p_s = bd.prove_sharded(ctx, pk, dz.data_ptr(), r, sr); e1.record(); barrier()
+            strong.append(max_over_ranks(e0.elapsed_time(e1)))
+            assert p_s == p_ref
+        if rank == 0:
+            assert p_ref == ctx.prove_device(pk, dz.data_ptr(), r, sr), "sharded proof differs from the single-GPU proof"
+            line["one_proof_sharded"] = {"n_gpus": world, "prove_s": min(strong) / 1e3, "all_s": [t / 1e3 for t in strong], "scaling": "strong",
+                                         "how": "every rank runs the witness map and reduces 1/N of each of the five queries (b2g16_prove_partial); all_gather of N x 576 B over NCCL; b2g16_prove_assemble",
+                                         "speedup_vs_1gpu_step": (ms / args.steps) / min(strong)}
     pk.free()
     del dz, hz
     if rank == 0 and not args.skip_standalone:

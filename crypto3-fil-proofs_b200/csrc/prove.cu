@@ -259,11 +259,21 @@ struct MsmOut { uint8_t a[96], b1[96], l[96], h[96], b2[192]; };
 
 // abc_host: optional {a32, b32, c32} host evaluations supplied by the caller's synthesis (b2g16_prove_abc);
 // otherwise a, b, c come from the key's CSR matrices.
+static void assemble_proof(const b2g16_pk* pk, const MsmOut& out, const uint8_t* r32, const uint8_t* s32, uint8_t* proof_out, b2g16_trace* tr);
+
+// part / parts: this call reduces only the contiguous slice [part n / parts, (part+1) n / parts) of each of the
+// five queries (one proof spread over several GPUs, b2g16_prove_partial); partial_out then receives the five
+// partial sums and no proof is assembled.
 static void prove_one(Ctx* c, const b2g16_pk* pk, const uint8_t* d_z_canon, const uint8_t* r32, const uint8_t* s32,
-                      uint8_t* proof_out, b2g16_trace* tr, const uint8_t* const* abc_host = nullptr) {
-    bool ok = true;
-    const Fr r = host_fr_from_bytes(r32, &ok), s = host_fr_from_bytes(s32, &ok);
-    B2_REQUIRE(ok, B2G16_E_NOT_CANONICAL, "r / s not canonical");
+                      uint8_t* proof_out, b2g16_trace* tr, const uint8_t* const* abc_host = nullptr,
+                      unsigned part = 0, unsigned parts = 1, MsmOut* partial_out = nullptr) {
+    if (!partial_out) {
+        bool ok = true;
+        host_fr_from_bytes(r32, &ok); host_fr_from_bytes(s32, &ok);
+        B2_REQUIRE(ok, B2G16_E_NOT_CANONICAL, "r / s not canonical");
+    }
+    auto lo_of = [&](uint64_t n) { return (size_t)(n * part / parts); };
+    auto cnt_of = [&](uint64_t n) { return (size_t)(n * (part + 1) / parts - n * part / parts); };
     const uint64_t m = pk->m, nv = pk->n_vars;
     cudaStream_t st = c->stream;
     cudaEvent_t ev[5];
@@ -308,20 +318,32 @@ static void prove_one(Ctx* c, const b2g16_pk* pk, const uint8_t* d_z_canon, cons
     // scratch at 2^27 and the integer pipe serialises them anyway; below, they overlap the NTT chain
     const bool serial = pk->log_m > 24;
     cudaStream_t s_b2 = serial ? st : c->aux[0], s_a = serial ? st : c->aux[1], s_b1 = serial ? st : c->aux[2], s_l = serial ? st : c->aux[3];
-    msm_g2_dev(c, pk->b_g2, zc, nv, o + offsetof(MsmOut, b2), s_b2, 0);
-    msm_g1_dev(c, pk->a, zc, nv, o + offsetof(MsmOut, a), s_a, 0);
-    msm_g1_dev(c, pk->b_g1, zc, nv, o + offsetof(MsmOut, b1), s_b1, 0);
-    msm_g1_dev(c, pk->l, zc + 8 * (1 + pk->n_in), pk->n_aux, o + offsetof(MsmOut, l), s_l, 0);
+    msm_g2_dev(c, pk->b_g2 + lo_of(nv), zc + 8 * lo_of(nv), cnt_of(nv), o + offsetof(MsmOut, b2), s_b2, 0);
+    msm_g1_dev(c, pk->a + lo_of(nv), zc + 8 * lo_of(nv), cnt_of(nv), o + offsetof(MsmOut, a), s_a, 0);
+    msm_g1_dev(c, pk->b_g1 + lo_of(nv), zc + 8 * lo_of(nv), cnt_of(nv), o + offsetof(MsmOut, b1), s_b1, 0);
+    msm_g1_dev(c, pk->l + lo_of(pk->n_aux), zc + 8 * (1 + pk->n_in + lo_of(pk->n_aux)), cnt_of(pk->n_aux), o + offsetof(MsmOut, l), s_l, 0);
     h_from_abc_dev(c, a.get(), b.get(), cc.get(), (int)pk->log_m, h.get(), false, nullptr);
     B2_CUDA(cudaEventRecord(ev[3], st));
-    msm_g1_dev(c, pk->h, h.get(), m - 1, o + offsetof(MsmOut, h), st, 0);
+    msm_g1_dev(c, pk->h + lo_of(m - 1), h.get() + 8 * lo_of(m - 1), cnt_of(m - 1), o + offsetof(MsmOut, h), st, 0);
     for (int i = 0; i < 4; ++i) { B2_CUDA(cudaEventRecord(c->ev_join[i], c->aux[i])); B2_CUDA(cudaStreamWaitEvent(st, c->ev_join[i], 0)); }
     B2_CUDA(cudaMemcpyAsync(&out, o, sizeof(MsmOut), cudaMemcpyDeviceToHost, st));
     if (tr && tr->h) B2_CUDA(cudaMemcpyAsync(tr->h, h.get(), m * 32, cudaMemcpyDeviceToHost, st));
     B2_CUDA(cudaEventRecord(ev[4], st));
     bad.check("assignment");                              // synchronises the stream
+    if (tr) {
+        for (int i = 0; i < 8; ++i) tr->stage_ms[i] = 0.f;
+        for (int i = 0; i < 4; ++i) cudaEventElapsedTime(&tr->stage_ms[i], ev[i], ev[i + 1]);   // ingest, abc, ntt/h, msm_h + join of the rest
+    }
+    for (auto& e : ev) cudaEventDestroy(e);
+    if (partial_out) { *partial_out = out; return; }
+    assemble_proof(pk, out, r32, s32, proof_out, tr);
+}
 
-    // host assembly
+// host assembly from the five multiexp results
+static void assemble_proof(const b2g16_pk* pk, const MsmOut& out, const uint8_t* r32, const uint8_t* s32, uint8_t* proof_out, b2g16_trace* tr) {
+    bool ok = true;
+    const Fr r = host_fr_from_bytes(r32, &ok), s = host_fr_from_bytes(s32, &ok);
+    B2_REQUIRE(ok, B2G16_E_NOT_CANONICAL, "r / s not canonical");
     G1Xyzz Abar = G1Xyzz::from_affine(host_g1_from_bytes(out.a)), B1bar = G1Xyzz::from_affine(host_g1_from_bytes(out.b1));
     G1Xyzz Lbar = G1Xyzz::from_affine(host_g1_from_bytes(out.l)), Hbar = G1Xyzz::from_affine(host_g1_from_bytes(out.h));
     G2Xyzz B2bar = G2Xyzz::from_affine(host_g2_from_bytes(out.b2));
@@ -343,10 +365,7 @@ static void prove_one(Ctx* c, const b2g16_pk* pk, const uint8_t* d_z_canon, cons
         if (tr->A) host_g1_to_bytes(Aa, tr->A);
         if (tr->B) host_g2_to_bytes(Ba, tr->B);
         if (tr->C) host_g1_to_bytes(Ca, tr->C);
-        for (int i = 0; i < 8; ++i) tr->stage_ms[i] = 0.f;
-        for (int i = 0; i < 4; ++i) cudaEventElapsedTime(&tr->stage_ms[i], ev[i], ev[i + 1]);   // ingest, abc, ntt/h, msm_h + join of the rest
     }
-    for (auto& e : ev) cudaEventDestroy(e);
 }
 
 }  // namespace b2
@@ -542,6 +561,39 @@ int b2g16_prove_abc(b2g16_ctx* hctx, const b2g16_pk* pk, const uint8_t* a32, con
         B2_CUDA(cudaMemcpyAsync(dz.get(), assignment32, pk->n_vars * 32, cudaMemcpyHostToDevice, c->stream));
         const uint8_t* abc[3] = {a32, b32, c32};
         prove_one(c, pk, dz.get(), r32, s32, proof_out, trace, abc);
+    });
+}
+
+// One proof over `parts` GPUs (latency mode): each rank, holding the whole key and witness,
+// runs the witness map and reduces its slice of the five queries; the host gathers parts x 576 bytes
+// (msm_a 96, msm_b1 96, msm_l 96, msm_h 96, msm_b2 192) and any rank assembles.
+int b2g16_prove_partial(b2g16_ctx* hctx, const b2g16_pk* pk, const uint8_t* d_assignment32, unsigned part, unsigned parts, uint8_t partials_out[576]) {
+    Ctx* c = reinterpret_cast<Ctx*>(hctx);
+    if (!c || !pk || !d_assignment32 || !partials_out || parts == 0 || part >= parts) return B2G16_E_INVALID_ARG;
+    static_assert(sizeof(MsmOut) == 576, "partial layout");
+    return guard(c, [&] {
+        MsmOut out;
+        prove_one(c, pk, d_assignment32, nullptr, nullptr, nullptr, nullptr, nullptr, part, parts, &out);
+        memcpy(partials_out, &out, sizeof out);
+    });
+}
+int b2g16_prove_assemble(b2g16_ctx* hctx, const b2g16_pk* pk, const uint8_t* partials, unsigned parts, const uint8_t r32[32], const uint8_t s32[32],
+                         uint8_t proof_out[192]) {
+    Ctx* c = reinterpret_cast<Ctx*>(hctx);
+    if (!c || !pk || !partials || parts == 0 || !r32 || !s32 || !proof_out) return B2G16_E_INVALID_ARG;
+    return guard(c, [&] {
+        G1Xyzz g1[4] = {G1Xyzz::identity(), G1Xyzz::identity(), G1Xyzz::identity(), G1Xyzz::identity()};
+        G2Xyzz g2 = G2Xyzz::identity();
+        for (unsigned k = 0; k < parts; ++k) {
+            const uint8_t* p = partials + (size_t)k * sizeof(MsmOut);
+            for (int q = 0; q < 4; ++q) g1[q].add_mixed(host_g1_from_bytes(p + 96 * q));
+            g2.add_mixed(host_g2_from_bytes(p + 384));
+        }
+        MsmOut sum;
+        host_g1_to_bytes(g1[0].to_affine(), sum.a); host_g1_to_bytes(g1[1].to_affine(), sum.b1);
+        host_g1_to_bytes(g1[2].to_affine(), sum.l); host_g1_to_bytes(g1[3].to_affine(), sum.h);
+        host_g2_to_bytes(g2.to_affine(), sum.b2);
+        assemble_proof(pk, sum, r32, s32, proof_out, nullptr);
     });
 }
 

@@ -83,6 +83,15 @@ def prove_partitions(ctx, pk, assignments, rs, ss, group=None):
     return gather_proofs(local, len(assignments), group)
 
 
+def prove_sharded(ctx, pk, d_assignment_ptr, r, s, group=None):
+    """One proof over all ranks of the group (latency mode): every rank holds the key and the
+    witness on its device, reduces its slice of the five queries (b2g16_prove_partial), the 576-byte partial
+    sets are all-gathered and every rank assembles the same 192 bytes (b2g16_prove_assemble)."""
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    part = ctx.prove_partial(pk, d_assignment_ptr, rank, world)
+    return ctx.prove_assemble(pk, all_gather_bytes(part, group), r, s)
+
+
 # ------------------------------------------------------------------ sharded Fr transform
 # One evaluation-domain transform of size N = 2^log_n over G ranks (SURVEY 8e row 3; replaces a
 # single crypto3-math evaluation_domain<Fr>::fft / inverse_fft call when the vector is spread over

@@ -417,6 +417,17 @@ class Context:
         self._chk(load().b2g16_prove_device(self.h, pk.h, C.c_void_p(d_assignment_ptr), _p(_u8(r)), _p(_u8(s)), int(priority), _p(proof), None))
         return proof.tobytes()
 
+    def prove_partial(self, pk, d_assignment_ptr, part, parts):
+        out = np.zeros(576, dtype=np.uint8)
+        self._chk(load().b2g16_prove_partial(self.h, pk.h, C.c_void_p(d_assignment_ptr), C.c_uint(part), C.c_uint(parts), _p(out)))
+        return out
+
+    def prove_assemble(self, pk, partials, r, s):
+        p = _u8(partials, 576)
+        proof = np.zeros(192, dtype=np.uint8)
+        self._chk(load().b2g16_prove_assemble(self.h, pk.h, _p(p), C.c_uint(p.shape[0]), _p(_u8(r)), _p(_u8(s)), _p(proof)))
+        return proof.tobytes()
+
     def prove_batch(self, pk, assignments, rs, ss, priority=False):
         z = _u8(assignments)
         n = _u8(rs, 32).shape[0]

@@ -179,6 +179,14 @@ int b2g16_prove(b2g16_ctx*, const b2g16_pk*, const uint8_t* assignment32, const 
 /* assignment already on the device; proof written to host */
 int b2g16_prove_device(b2g16_ctx*, const b2g16_pk*, const uint8_t* d_assignment32, const uint8_t r32[32],
                        const uint8_t s32[32], int priority, uint8_t proof_out[192], b2g16_trace* trace);
+/* One proof spread over `parts` GPUs (latency mode; what C4's single WindowPoSt partition needs
+ * to use more than one GPU): every rank holds the key and the witness, runs the witness map and reduces only the
+ * contiguous slice [part n/parts, (part+1) n/parts) of each of the five queries.  partials_out: msm_a(96) msm_b1(96)
+ * msm_l(96) msm_h(96) msm_b2(192).  The host gathers parts x 576 bytes (an all-gather) and b2g16_prove_assemble
+ * sums them and builds the same 192 bytes b2g16_prove would. */
+int b2g16_prove_partial(b2g16_ctx*, const b2g16_pk*, const uint8_t* d_assignment32, unsigned part, unsigned parts, uint8_t partials_out[576]);
+int b2g16_prove_assemble(b2g16_ctx*, const b2g16_pk*, const uint8_t* partials, unsigned parts, const uint8_t r32[32],
+                         const uint8_t s32[32], uint8_t proof_out[192]);
 /* n_partitions independent witnesses for one key -> 192*n bytes (multi_proof, F/api/seal.hpp:304-308) */
 int b2g16_prove_batch(b2g16_ctx*, const b2g16_pk*, const uint8_t* assignments32, size_t n_partitions,
                       const uint8_t* r32s, const uint8_t* s32s, int priority, uint8_t* proofs_out);

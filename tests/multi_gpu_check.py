@@ -4,6 +4,7 @@ Every rank compares the sharded results with the same computation done whole on 
   * b2g16.dist.ntt_sharded (forward / inverse x coset x natural / cyclic order) against b2g16_ntt_device
     of the full vector, bit for bit;
   * b2g16.dist.msm_resident_sharded against the full multiexp;
+  * b2g16.dist.prove_sharded: one proof with the five multiexps range-sharded over the ranks equals b2g16_prove's;
   * b2g16.dist.prove_partitions: 2 N + 1 partitions under one key, the gathered 192 (2N+1)-byte multi-proof
     equals the proofs made one by one and passes b2g16_verify_batch.
 tests/test_gpu_verify.py-style pytest wrapper: tests/test_gpu_multi.py (skips with fewer than 2 GPUs)."""
@@ -100,6 +101,10 @@ def main():
     multi = bd.prove_partitions(ctx, pk, zs, rs, ss)
     assert len(multi) == 192 * n_part
     assert multi == b"".join(ctx.prove(pk, zs[k], rs[k], ss[k]) for k in range(n_part)), ("multi-proof", rank)
+    # one proof spread over all ranks: same 192 bytes as the single-GPU prover
+    dz0 = torch.from_numpy(zs[0]).to(dev)
+    assert bd.prove_sharded(ctx, pk, dz0.data_ptr(), rs[0], ss[0]) == multi[:192], ("prove_sharded", rank)
+    checks += 1
     pvk = ctx.vk_prepare(vk)
     assert ctx.verify_batch(pvk, np.stack([z[1:1 + s.n_in] for z in zs]), multi)
     checks += 2
