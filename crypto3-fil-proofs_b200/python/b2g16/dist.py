@@ -92,6 +92,63 @@ def prove_sharded(ctx, pk, d_assignment_ptr, r, s, group=None):
     return ctx.prove_assemble(pk, all_gather_bytes(part, group), r, s)
 
 
+def partition_schedule(n_partitions, world):
+    """Waves of a multi-partition proof on `world` GPUs (C5 = 10 partitions on 8 GPUs).
+    Full waves run one partition per GPU; the remaining R < world partitions are each spread over a group of
+    world // R' GPUs (R' = R rounded up to a power of two) instead of leaving world - R GPUs idle.
+    Returns [(partition, [ranks])] in execution order; entries of one wave are consecutive."""
+    out, k = [], 0
+    while n_partitions - k >= world:
+        out += [(k + r, [r]) for r in range(world)]
+        k += world
+    rem = n_partitions - k
+    if rem:
+        groups = 1
+        while groups < rem:
+            groups *= 2
+        size = max(1, world // groups)
+        out += [(k + g, list(range(g * size, (g + 1) * size))) for g in range(rem)]
+    return out
+
+
+class PartitionScheduler:
+    """Creates the sub-groups of partition_schedule once (collective: every rank must construct it) and proves
+    all partitions; d_assignment_for(k) returns the device pointer of partition k's witness on this rank (it is
+    called only for partitions this rank takes part in)."""
+
+    def __init__(self, n_partitions, group=None):
+        self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
+        self.n = n_partitions
+        self.plan = partition_schedule(n_partitions, self.world)
+        self.groups = {}
+        for k, ranks in self.plan:
+            if len(ranks) > 1 and tuple(ranks) not in self.groups:
+                self.groups[tuple(ranks)] = dist.new_group(ranks=ranks)        # every rank calls new_group for every group
+        self.parent = group
+
+    def prove_all(self, ctx, pk, d_assignment_for, rs, ss):
+        local = {}
+        for k, ranks in self.plan:
+            if self.rank not in ranks:
+                continue
+            if len(ranks) == 1:
+                local[k] = ctx.prove_device(pk, d_assignment_for(k), rs[k], ss[k])
+            else:
+                local[k] = prove_sharded(ctx, pk, d_assignment_for(k), rs[k], ss[k], group=self.groups[tuple(ranks)])
+        # owner of partition k for the gather = first rank of its group
+        per = max(sum(1 for k, ranks in self.plan if ranks[0] == r) for r in range(self.world))
+        buf = np.zeros((max(per, 1), 192), dtype=np.uint8)
+        slot_of, counters = {}, [0] * self.world
+        for k, ranks in self.plan:
+            slot_of[k] = (ranks[0], counters[ranks[0]])
+            counters[ranks[0]] += 1
+        for k, (owner, slot) in slot_of.items():
+            if owner == self.rank:
+                buf[slot] = np.frombuffer(local[k], dtype=np.uint8)
+        allb = all_gather_bytes(buf, self.parent)
+        return b"".join(allb[slot_of[k][0], slot_of[k][1]].tobytes() for k in range(self.n))
+
+
 # ------------------------------------------------------------------ sharded Fr transform
 # One evaluation-domain transform of size N = 2^log_n over G ranks (SURVEY 8e row 3; replaces a
 # single crypto3-math evaluation_domain<Fr>::fft / inverse_fft call when the vector is spread over

@@ -105,6 +105,19 @@ def main():
     dz0 = torch.from_numpy(zs[0]).to(dev)
     assert bd.prove_sharded(ctx, pk, dz0.data_ptr(), rs[0], ss[0]) == multi[:192], ("prove_sharded", rank)
     checks += 1
+    # scheduled multi-proof: full waves one partition per GPU, the remainder spread over sub-groups
+    sched = bd.PartitionScheduler(n_part)
+    dzs = {}
+
+    def d_for(k):
+        dzs[k] = torch.from_numpy(zs[k]).to(dev)
+        return dzs[k].data_ptr()
+    assert sched.prove_all(ctx, pk, d_for, rs, ss) == multi, ("scheduled multi-proof", rank)
+    if world >= 4:
+        n3 = world + world // 2                                       # remainder world/2 -> groups of 2
+        sched3 = bd.PartitionScheduler(n3)
+        assert sched3.prove_all(ctx, pk, d_for, rs, ss) == multi[:192 * n3], ("scheduled multi-proof, groups of 2", rank)
+    checks += 1
     pvk = ctx.vk_prepare(vk)
     assert ctx.verify_batch(pvk, np.stack([z[1:1 + s.n_in] for z in zs]), multi)
     checks += 2

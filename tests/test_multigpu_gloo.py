@@ -58,6 +58,24 @@ def test_shard_ranges_cover_everything():
     assert bd.my_partitions(10, 1, 8) == [1, 9]
 
 
+def test_partition_schedule():
+    sys.path.insert(0, os.path.join(ROOT, "crypto3-fil-proofs_b200", "python"))
+    from b2g16 import dist as bd
+    # C5: 10 partitions on 8 GPUs -> one full wave, then 2 partitions on 4 GPUs each
+    plan = bd.partition_schedule(10, 8)
+    assert plan[:8] == [(k, [k]) for k in range(8)]
+    assert plan[8:] == [(8, [0, 1, 2, 3]), (9, [4, 5, 6, 7])]
+    assert bd.partition_schedule(1, 8) == [(0, list(range(8)))]                 # C4: one partition, all GPUs
+    assert bd.partition_schedule(3, 8) == [(0, [0, 1]), (1, [2, 3]), (2, [4, 5])]
+    assert bd.partition_schedule(5, 2) == [(0, [0]), (1, [1]), (2, [0]), (3, [1]), (4, [0, 1])]
+    assert bd.partition_schedule(4, 1) == [(k, [0]) for k in range(4)]
+    for p in range(0, 20):
+        for w in (1, 2, 4, 8):
+            plan = bd.partition_schedule(p, w)
+            assert [k for k, _ in plan] == list(range(p))
+            assert all(0 <= r < w for _, ranks in plan for r in ranks)
+
+
 def test_world_size_2_gloo(oracle):
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
