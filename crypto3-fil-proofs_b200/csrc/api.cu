@@ -34,6 +34,8 @@ int b2g16_init(int device, void* stream, b2g16_ctx** out) {
         B2_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
         if (const char* e = getenv("B2G16_MSM_C")) c->msm_window_override = atoi(e);
         if (const char* e = getenv("B2G16_ACC_VARIANT")) c->acc_variant = atoi(e);
+        if (const char* e = getenv("B2G16_SERIAL_LOG")) c->serial_above_log = atoi(e);
+        if (const char* e = getenv("B2G16_RED_LOG")) { int v = atoi(e); if (v >= 1 && v <= 6) c->red_log = v; }
         ntt_init_roots(c);
     });
     if (rc != B2G16_OK) { delete c; return rc; }

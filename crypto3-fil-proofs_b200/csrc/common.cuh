@@ -30,6 +30,8 @@ struct Ctx {
     float msm_ms[5] = {0, 0, 0, 0, 0};  // last timed MSM: digits+hist, scan, scatter, accumulate, reduce
     bool time_msm = false;
     int msm_window_override = 0;        // 0 = pick by size
+    int serial_above_log = 24;          // proofs with a larger domain run their five multiexps one after the other (B2G16_SERIAL_LOG)
+    int red_log = 3;                    // log2 of the items per thread and level in the bucket reduction (B2G16_RED_LOG)
     int acc_variant = 102;              // bucket-accumulation kernel variant (B2G16_ACC_VARIANT)
     void* fixed_base[2] = {nullptr, nullptr};   // generator tables (G1, G2), built on first use
 };

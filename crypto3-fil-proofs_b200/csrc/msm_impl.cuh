@@ -425,9 +425,12 @@ template <class F> __global__ void __launch_bounds__(128) gen_mul_kernel(const A
 }
 
 // ---- host driver ---------------------------------------------------------------------
-// Window width by size (measured on B200, uniform scalars, chunked accumulate): every window costs one
-// mixed addition per point, every bucket two full additions in the reduction and the counting-sort
-// scatter gets less local as buckets multiply -- 16 bits up to 2^22 points, 20 bits from 2^23.
+// Window width by size (measured on B200, uniform scalars, chunked accumulate): every window costs one mixed
+// addition per point, every bucket two full additions in the reduction, and the counting-sort scatter gets less
+// local as buckets multiply -- 16 bits up to 2^22 points, 20 bits from 2^23.  Standalone, 17 bits is 1.5 % faster
+// for 2^20 .. 2^23 points (profiles/r01_window_sweep2_g{1,2}.jsonl), but inside a proof it moves the G2 multiexp
+// onto the chunked kernel, whose few long CTAs co-schedule badly with the other four multiexps running on
+// sibling streams (2^22 proof: 0.261 s against 0.241 s), so the proof-friendly choice stays.
 inline int msm_pick_window(size_t n) {
     int lg = 0;
     while (((size_t)1 << (lg + 1)) <= n) ++lg;
@@ -508,7 +511,11 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
     DevBuf<uint32_t> hist(nb + 1, st), off(nb + 1, st), cursor(nb + 1, st), seg_off(chunked ? 0 : nb + 1, st), tile_sums((size_t)n_tiles + 1, st), sorted(max_entries, st);
     DevBuf<Xyzz<F>> seg_acc(chunked ? nb : max_segs, st), pieces(2 * (size_t)n_chunks, st);
     DevBuf<uint32_t> piece_bucket(2 * (size_t)n_chunks, st);
-    constexpr uint32_t RED_PER = 32;                                   // items per thread and level in the bucket reduction
+    // items per thread and level in the bucket reduction (tuning knob B2G16_RED_LOG, default 2^3): the reduction is
+    // latency-bound (a chain of 2 * RED_PER dependent additions per thread and level), so short chains on many
+    // threads beat long chains on few
+    const int red_log = ctx->red_log;
+    const uint32_t RED_PER = 1u << red_log;
     const uint32_t T1 = (B + 1 + RED_PER - 1) / RED_PER;
     DevBuf<Xyzz<F>> red_a[2] = {DevBuf<Xyzz<F>>((size_t)W * T1, st), DevBuf<Xyzz<F>>((size_t)W * T1, st)};
     DevBuf<Xyzz<F>> red_r[2] = {DevBuf<Xyzz<F>>((size_t)W * T1, st), DevBuf<Xyzz<F>>((size_t)W * T1, st)};
@@ -563,7 +570,7 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
             ctx->launches++;
             a_in = red_a[side].get(); r_in = red_r[side].get();
             if (T == 1) break;
-            count = T; stride = T; log_s += 5; shift_one = 0; side ^= 1;
+            count = T; stride = T; log_s += red_log; shift_one = 0; side ^= 1;
         }
         win = a_in;
     } else {

@@ -317,7 +317,7 @@ static void prove_one(Ctx* c, const b2g16_pk* pk, const uint8_t* d_z_canon, cons
     uint8_t* o = d_out.get();
     // above 2^24 the witness MSMs run one after the other on the main stream: each needs ~9 GB of sort
     // scratch at 2^27 and the integer pipe serialises them anyway; below, they overlap the NTT chain
-    const bool serial = pk->log_m > 24;
+    const bool serial = (int)pk->log_m > c->serial_above_log;
     cudaStream_t s_b2 = serial ? st : c->aux[0], s_a = serial ? st : c->aux[1], s_b1 = serial ? st : c->aux[2], s_l = serial ? st : c->aux[3];
     msm_g2_dev(c, pk->b_g2 + lo_of(nv), zc + 8 * lo_of(nv), cnt_of(nv), o + offsetof(MsmOut, b2), s_b2, 0);
     msm_g1_dev(c, pk->a + lo_of(nv), zc + 8 * lo_of(nv), cnt_of(nv), o + offsetof(MsmOut, a), s_a, 0);
