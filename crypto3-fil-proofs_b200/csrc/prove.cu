@@ -50,6 +50,37 @@ __global__ void __launch_bounds__(256) abc_spmv_kernel(DevCsr A, DevCsr B, DevCs
         fr_store(a + i, sa); fr_store(b + i, sb); fr_store(c + i, sc);
     }
 }
+// The same evaluations for the rows row0 + stride * k, k < count, written as canonical scalars: a rank's share
+// of a, b, c when the witness map of one proof is spread over several GPUs (cyclic row distribution, which is
+// what the sharded inverse transform consumes; b2g16.dist.prove_sharded_full).
+__global__ void __launch_bounds__(256) abc_spmv_strided_kernel(DevCsr A, DevCsr B, DevCsr C, const Fr* __restrict__ z, uint64_t n_cons, uint64_t n_in,
+                                                               uint64_t row0, uint64_t stride, uint64_t count, Fr* __restrict__ a, Fr* __restrict__ b, Fr* __restrict__ c) {
+    for (uint64_t k = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; k < count; k += (uint64_t)gridDim.x * blockDim.x) {
+        const uint64_t i = row0 + stride * k;
+        Fr sa = Fr::zero(), sb = Fr::zero(), sc = Fr::zero();
+        if (i < n_cons) {
+            for (uint32_t q = A.row_ptr[i]; q < A.row_ptr[i + 1]; ++q) sa = sa + fr_load(A.val + q) * fr_load(z + A.col[q]);
+            for (uint32_t q = B.row_ptr[i]; q < B.row_ptr[i + 1]; ++q) sb = sb + fr_load(B.val + q) * fr_load(z + B.col[q]);
+            for (uint32_t q = C.row_ptr[i]; q < C.row_ptr[i + 1]; ++q) sc = sc + fr_load(C.val + q) * fr_load(z + C.col[q]);
+        } else if (i - n_cons <= n_in) {
+            sa = fr_load(z + (i - n_cons));
+        }
+        Fr t;
+        sa.to_canonical(t.v); fr_store(a + k, t);
+        sb.to_canonical(t.v); fr_store(b + k, t);
+        sc.to_canonical(t.v); fr_store(c + k, t);
+    }
+}
+// out = (a * b - c) * zinv on canonical scalars (the quotient by Z on the coset, pointwise; any distribution)
+__global__ void __launch_bounds__(256) h_pointwise_kernel(const Fr* __restrict__ a, const Fr* __restrict__ b, const Fr* __restrict__ c, uint64_t count, Fr zinv,
+                                                          Fr* __restrict__ out) {
+    for (uint64_t k = blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; k < count; k += (uint64_t)gridDim.x * blockDim.x) {
+        // canonical x is the Montgomery form of x/R: (a R^2 -> Montgomery a) * b -> canonical a b; a product with a
+        // Montgomery-form constant keeps a canonical operand canonical
+        const Fr ab = (fr_load(a + k) * Fr::r2()) * fr_load(b + k);
+        fr_store(out + k, (ab - fr_load(c + k)) * zinv);
+    }
+}
 // one layer of the forward-built synthetic instance: z[out0 + i] = (A_i . z)(B_i . z), rows [r0, r1)
 __global__ void __launch_bounds__(256) synth_layer_kernel(DevCsr A, DevCsr B, Fr* __restrict__ z, uint64_t r0, uint64_t r1, uint64_t out0) {
     for (uint64_t i = r0 + blockIdx.x * (uint64_t)blockDim.x + threadIdx.x; i < r1; i += (uint64_t)gridDim.x * blockDim.x) {
@@ -267,7 +298,8 @@ static void assemble_proof(const b2g16_pk* pk, const MsmOut& out, const uint8_t*
 // partial sums and no proof is assembled.
 static void prove_one(Ctx* c, const b2g16_pk* pk, const uint8_t* d_z_canon, const uint8_t* r32, const uint8_t* s32,
                       uint8_t* proof_out, b2g16_trace* tr, const uint8_t* const* abc_host = nullptr,
-                      unsigned part = 0, unsigned parts = 1, MsmOut* partial_out = nullptr) {
+                      unsigned part = 0, unsigned parts = 1, MsmOut* partial_out = nullptr,
+                      const uint8_t* d_h_slice = nullptr, uint64_t h_first = 0, uint64_t h_count = 0) {
     if (!partial_out) {
         bool ok = true;
         host_fr_from_bytes(r32, &ok); host_fr_from_bytes(s32, &ok);
@@ -280,14 +312,19 @@ static void prove_one(Ctx* c, const b2g16_pk* pk, const uint8_t* d_z_canon, cons
     cudaEvent_t ev[5];
     for (auto& e : ev) B2_CUDA(cudaEventCreate(&e));
     DevFlag bad(c);
-    DevBuf<Fr> z(nv, st), a(m, st), b(m, st), cc(m, st);
-    DevBuf<uint32_t> h(m * 8, st);
+    // d_h_slice: H coefficients [h_first, h_first + h_count) computed elsewhere (the sharded witness map): no
+    // constraint evaluation and no transforms here, and this rank's share of the H query is exactly that range
+    const bool ext_h = d_h_slice != nullptr;
+    DevBuf<Fr> z(ext_h ? 0 : nv, st), a(ext_h ? 0 : m, st), b(ext_h ? 0 : m, st), cc(ext_h ? 0 : m, st);
+    DevBuf<uint32_t> h(ext_h ? 0 : m * 8, st);
     DevBuf<uint8_t> d_out(sizeof(MsmOut), st);
     MsmOut out;
     B2_CUDA(cudaEventRecord(ev[0], st));
-    fr_from_bytes_dev(c, d_z_canon, z.get(), nv, bad.ptr());
+    if (ext_h) scalars_check_dev(c, d_z_canon, nv, bad.ptr());
+    else fr_from_bytes_dev(c, d_z_canon, z.get(), nv, bad.ptr());
     B2_CUDA(cudaEventRecord(ev[1], st));
-    if (abc_host) {
+    if (ext_h) {
+    } else if (abc_host) {
         Fr* dst[3] = {a.get(), b.get(), cc.get()};
         for (int i = 0; i < 3; ++i) {                                 // same size: upload, then convert in place
             B2_CUDA(cudaMemcpyAsync(dst[i], abc_host[i], m * 32, cudaMemcpyHostToDevice, st));
@@ -323,12 +360,17 @@ static void prove_one(Ctx* c, const b2g16_pk* pk, const uint8_t* d_z_canon, cons
     msm_g1_dev(c, pk->a + lo_of(nv), zc + 8 * lo_of(nv), cnt_of(nv), o + offsetof(MsmOut, a), s_a, 0);
     msm_g1_dev(c, pk->b_g1 + lo_of(nv), zc + 8 * lo_of(nv), cnt_of(nv), o + offsetof(MsmOut, b1), s_b1, 0);
     msm_g1_dev(c, pk->l + lo_of(pk->n_aux), zc + 8 * (1 + pk->n_in + lo_of(pk->n_aux)), cnt_of(pk->n_aux), o + offsetof(MsmOut, l), s_l, 0);
-    h_from_abc_dev(c, a.get(), b.get(), cc.get(), (int)pk->log_m, h.get(), false, nullptr);
+    if (!ext_h) h_from_abc_dev(c, a.get(), b.get(), cc.get(), (int)pk->log_m, h.get(), false, nullptr);
     B2_CUDA(cudaEventRecord(ev[3], st));
-    msm_g1_dev(c, pk->h + lo_of(m - 1), h.get() + 8 * lo_of(m - 1), cnt_of(m - 1), o + offsetof(MsmOut, h), st, 0);
+    if (ext_h) {
+        const uint64_t hi = h_first + h_count < m - 1 ? h_first + h_count : m - 1;       // h_{m-1} = 0 has no base
+        const uint64_t cnt = hi > h_first ? hi - h_first : 0;
+        msm_g1_dev(c, pk->h + h_first, reinterpret_cast<const uint32_t*>(d_h_slice), cnt, o + offsetof(MsmOut, h), st, 0);
+    } else
+        msm_g1_dev(c, pk->h + lo_of(m - 1), h.get() + 8 * lo_of(m - 1), cnt_of(m - 1), o + offsetof(MsmOut, h), st, 0);
     for (int i = 0; i < 4; ++i) { B2_CUDA(cudaEventRecord(c->ev_join[i], c->aux[i])); B2_CUDA(cudaStreamWaitEvent(st, c->ev_join[i], 0)); }
     B2_CUDA(cudaMemcpyAsync(&out, o, sizeof(MsmOut), cudaMemcpyDeviceToHost, st));
-    if (tr && tr->h) B2_CUDA(cudaMemcpyAsync(tr->h, h.get(), m * 32, cudaMemcpyDeviceToHost, st));
+    if (tr && tr->h && !ext_h) B2_CUDA(cudaMemcpyAsync(tr->h, h.get(), m * 32, cudaMemcpyDeviceToHost, st));
     B2_CUDA(cudaEventRecord(ev[4], st));
     bad.check("assignment");                              // synchronises the stream
     if (tr) {
@@ -590,6 +632,56 @@ int b2g16_prove_partial(b2g16_ctx* hctx, const b2g16_pk* pk, const uint8_t* d_as
     return guard(c, [&] {
         MsmOut out;
         prove_one(c, pk, d_assignment32, nullptr, nullptr, nullptr, nullptr, nullptr, part, parts, &out);
+        memcpy(partials_out, &out, sizeof out);
+    });
+}
+// Pieces of a proof whose witness map is spread over the ranks as well (b2g16.dist.prove_sharded_full):
+//   abc_evals_strided: this rank's rows row0 + stride k of a, b, c as canonical scalars
+//   h_pointwise:       (a b - c) / Z on the coset, elementwise on canonical scalars
+//   prove_partial_h:   b2g16_prove_partial with the H coefficients [h_first, h_first + h_count) supplied by the caller
+int b2g16_abc_evals_strided_device(b2g16_ctx* hctx, const b2g16_pk* pk, const uint8_t* d_assignment32, uint64_t row0, uint64_t stride, uint64_t count,
+                                   uint8_t* d_a32, uint8_t* d_b32, uint8_t* d_c32) {
+    Ctx* c = reinterpret_cast<Ctx*>(hctx);
+    if (!c || !pk || !d_assignment32 || !d_a32 || !d_b32 || !d_c32 || stride == 0) return B2G16_E_INVALID_ARG;
+    return guard(c, [&] {
+        B2_REQUIRE(pk->A.row_ptr && pk->B.row_ptr && pk->C.row_ptr, B2G16_E_INVALID_ARG, "abc_evals: key was loaded without constraint matrices");
+        B2_REQUIRE(count == 0 || row0 + stride * (count - 1) < pk->m, B2G16_E_INVALID_ARG, "abc_evals: rows outside the domain");
+        DevFlag bad(c);
+        DevBuf<Fr> z(pk->n_vars, c->stream);
+        fr_from_bytes_dev(c, d_assignment32, z.get(), pk->n_vars, bad.ptr());
+        abc_spmv_strided_kernel<<<grid_for(count, 256), 256, 0, c->stream>>>(pk->A, pk->B, pk->C, z.get(), pk->n_cons, pk->n_in, row0, stride, count,
+                                                                              reinterpret_cast<Fr*>(d_a32), reinterpret_cast<Fr*>(d_b32), reinterpret_cast<Fr*>(d_c32));
+        c->launches++;
+        B2_CUDA(cudaGetLastError());
+        bad.check("assignment");
+    });
+}
+int b2g16_h_pointwise_device(b2g16_ctx* hctx, const uint8_t* d_a32, const uint8_t* d_b32, const uint8_t* d_c32, uint64_t count, unsigned log_m, uint8_t* d_out32) {
+    Ctx* c = reinterpret_cast<Ctx*>(hctx);
+    if (!c || !d_a32 || !d_b32 || !d_c32 || !d_out32 || log_m > 30) return B2G16_E_INVALID_ARG;
+    return guard(c, [&] {
+        Fr g = Fr::one(), seven = Fr::zero();
+        for (int i = 0; i < 7; ++i) seven = seven + Fr::one();
+        g = seven;
+        for (unsigned i = 0; i < log_m; ++i) g = g.sqr();                                   // g^(2^log_m)
+        const Fr zinv = (g - Fr::one()).inv();
+        h_pointwise_kernel<<<grid_for(count, 256), 256, 0, c->stream>>>(reinterpret_cast<const Fr*>(d_a32), reinterpret_cast<const Fr*>(d_b32),
+                                                                         reinterpret_cast<const Fr*>(d_c32), count, zinv, reinterpret_cast<Fr*>(d_out32));
+        c->launches++;
+        B2_CUDA(cudaGetLastError());
+    });
+}
+int b2g16_prove_partial_h(b2g16_ctx* hctx, const b2g16_pk* pk, const uint8_t* d_assignment32, unsigned part, unsigned parts, const uint8_t* d_h_slice32,
+                          uint64_t h_first, uint64_t h_count, uint8_t partials_out[576]) {
+    Ctx* c = reinterpret_cast<Ctx*>(hctx);
+    if (!c || !pk || !d_assignment32 || !partials_out || !d_h_slice32 || parts == 0 || part >= parts) return B2G16_E_INVALID_ARG;
+    return guard(c, [&] {
+        B2_REQUIRE(h_first + h_count <= pk->m, B2G16_E_INVALID_ARG, "prove_partial_h: H range outside the domain");
+        DevFlag bad(c);
+        scalars_check_dev(c, d_h_slice32, h_count, bad.ptr());
+        bad.check("H coefficients");
+        MsmOut out;
+        prove_one(c, pk, d_assignment32, nullptr, nullptr, nullptr, nullptr, nullptr, part, parts, &out, d_h_slice32, h_first, h_count);
         memcpy(partials_out, &out, sizeof out);
     });
 }

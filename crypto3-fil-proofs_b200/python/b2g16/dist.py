@@ -302,3 +302,25 @@ class PeerNtt:
         for p in self._own:
             self.ctx.peer_free(p)
         self._own = []
+
+
+def prove_sharded_full(ctx, pk, peer, d_assignment_ptr, r, s, group=None):
+    """One proof over all ranks with the witness map sharded as well (prove_sharded repeats it on every rank).
+    peer: a PeerNtt for the key's domain (log_n = log_m), built once and reused.  Rank k1 evaluates the rows
+    k1 + G k2 of a, b, c (the cyclic order the sharded inverse transform consumes), the seven transforms run on the
+    fused peer-memory path, the quotient by Z is pointwise, and the rank's block of H coefficients
+    [rank M, (rank + 1) M) is exactly its share of the H query."""
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    M, log_m = peer.M, peer.log_n
+    dev = peer.x.device
+    a, b, c = (torch.empty((M, 32), dtype=torch.uint8, device=dev) for _ in range(3))
+    ctx.abc_evals_strided_device(pk, d_assignment_ptr, rank, world, M, a.data_ptr(), b.data_ptr(), c.data_ptr())
+    for v in (a, b, c):
+        peer.y.copy_(v)
+        peer.inverse()                                   # evaluations on the domain -> coefficients (natural block)
+        peer.forward(coset=True)                         # -> evaluations on the coset g D (cyclic)
+        v.copy_(peer.y)
+    ctx.h_pointwise_device(a.data_ptr(), b.data_ptr(), c.data_ptr(), M, log_m, peer.y.data_ptr())
+    peer.inverse(coset=True)                             # -> H coefficients [rank M, (rank + 1) M)
+    part = ctx.prove_partial_h(pk, d_assignment_ptr, rank, world, peer.x.data_ptr(), rank * M, M)
+    return ctx.prove_assemble(pk, all_gather_bytes(part, group), r, s)

@@ -422,6 +422,19 @@ class Context:
         self._chk(load().b2g16_prove_partial(self.h, pk.h, C.c_void_p(d_assignment_ptr), C.c_uint(part), C.c_uint(parts), _p(out)))
         return out
 
+    def abc_evals_strided_device(self, pk, d_assignment_ptr, row0, stride, count, d_a, d_b, d_c):
+        self._chk(load().b2g16_abc_evals_strided_device(self.h, pk.h, C.c_void_p(d_assignment_ptr), C.c_uint64(row0), C.c_uint64(stride), C.c_uint64(count),
+                                                        C.c_void_p(d_a), C.c_void_p(d_b), C.c_void_p(d_c)))
+
+    def h_pointwise_device(self, d_a, d_b, d_c, count, log_m, d_out):
+        self._chk(load().b2g16_h_pointwise_device(self.h, C.c_void_p(d_a), C.c_void_p(d_b), C.c_void_p(d_c), C.c_uint64(count), C.c_uint(log_m), C.c_void_p(d_out)))
+
+    def prove_partial_h(self, pk, d_assignment_ptr, part, parts, d_h_ptr, h_first, h_count):
+        out = np.zeros(576, dtype=np.uint8)
+        self._chk(load().b2g16_prove_partial_h(self.h, pk.h, C.c_void_p(d_assignment_ptr), C.c_uint(part), C.c_uint(parts), C.c_void_p(d_h_ptr),
+                                               C.c_uint64(h_first), C.c_uint64(h_count), _p(out)))
+        return out
+
     def prove_assemble(self, pk, partials, r, s):
         p = _u8(partials, 576)
         proof = np.zeros(192, dtype=np.uint8)

@@ -185,6 +185,15 @@ int b2g16_prove_device(b2g16_ctx*, const b2g16_pk*, const uint8_t* d_assignment3
  * msm_l(96) msm_h(96) msm_b2(192).  The host gathers parts x 576 bytes (an all-gather) and b2g16_prove_assemble
  * sums them and builds the same 192 bytes b2g16_prove would. */
 int b2g16_prove_partial(b2g16_ctx*, const b2g16_pk*, const uint8_t* d_assignment32, unsigned part, unsigned parts, uint8_t partials_out[576]);
+/* The same with the witness map spread over the ranks too (b2g16.dist.prove_sharded_full shows the sequence): each
+ * rank evaluates its rows row0 + stride k of a, b, c (canonical scalars, cyclic distribution), the seven transforms
+ * run sharded (b2g16_ntt_cross_p2p_device + local transforms), (a b - c) / Z is pointwise, and the rank's block of H
+ * coefficients feeds its share of the H query directly. */
+int b2g16_abc_evals_strided_device(b2g16_ctx*, const b2g16_pk*, const uint8_t* d_assignment32, uint64_t row0, uint64_t stride, uint64_t count,
+                                   uint8_t* d_a32, uint8_t* d_b32, uint8_t* d_c32);
+int b2g16_h_pointwise_device(b2g16_ctx*, const uint8_t* d_a32, const uint8_t* d_b32, const uint8_t* d_c32, uint64_t count, unsigned log_m, uint8_t* d_out32);
+int b2g16_prove_partial_h(b2g16_ctx*, const b2g16_pk*, const uint8_t* d_assignment32, unsigned part, unsigned parts, const uint8_t* d_h_slice32,
+                          uint64_t h_first, uint64_t h_count, uint8_t partials_out[576]);
 int b2g16_prove_assemble(b2g16_ctx*, const b2g16_pk*, const uint8_t* partials, unsigned parts, const uint8_t r32[32],
                          const uint8_t s32[32], uint8_t proof_out[192]);
 /* n_partitions independent witnesses for one key -> 192*n bytes (multi_proof, F/api/seal.hpp:304-308) */

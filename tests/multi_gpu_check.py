@@ -118,6 +118,12 @@ def main():
         sched3 = bd.PartitionScheduler(n3)
         assert sched3.prove_all(ctx, pk, d_for, rs, ss) == multi[:192 * n3], ("scheduled multi-proof, groups of 2", rank)
     checks += 1
+    # ... and with the witness map sharded too (transforms on the fused peer-memory path)
+    pn = bd.PeerNtt(ctx, s.log_m)
+    assert bd.prove_sharded_full(ctx, pk, pn, dz0.data_ptr(), rs[0], ss[0]) == multi[:192], ("prove_sharded_full", rank)
+    assert bd.prove_sharded_full(ctx, pk, pn, d_for(1), rs[1], ss[1]) == multi[192:384], ("prove_sharded_full, reuse", rank)
+    pn.close()
+    checks += 1
     pvk = ctx.vk_prepare(vk)
     assert ctx.verify_batch(pvk, np.stack([z[1:1 + s.n_in] for z in zs]), multi)
     checks += 2

@@ -115,3 +115,44 @@ def test_proof_from_partial_sets(ctx, oracle, parts):
     with pytest.raises(lib.B2g16Error):
         ctx.prove_partial(pk, dz.data_ptr(), parts, parts)                       # part out of range
     pk.free()
+
+
+def test_witness_map_pieces_single_gpu(ctx, oracle):
+    """The device steps of b2g16.dist.prove_sharded_full with one 'rank': strided constraint evaluation, the
+    transform chain through the public transform entry point, the pointwise quotient, and the partial prove that
+    takes the H coefficients from outside -- every intermediate against the oracle's trace."""
+    s, cs, z = util.synth_instance(oracle, 10, 3, seed=17)
+    toxic, r, sr = util.toxic_from_seed(17)
+    pk = ctx.pk_generate(cs, toxic)
+    okey = oracle.groth16_setup(cs, toxic)
+    want, tr = oracle.groth16_prove(okey, z, r, sr, want_trace=True)
+    m, log_m = 1 << s.log_m, s.log_m
+    dz = torch.from_numpy(z).cuda()
+    a, b, c = (torch.empty((m, 32), dtype=torch.uint8, device="cuda") for _ in range(3))
+    ctx.abc_evals_strided_device(pk, dz.data_ptr(), 0, 1, m, a.data_ptr(), b.data_ptr(), c.data_ptr())
+    ctx.synchronize()
+    for got, name in ((a, "a"), (b, "b"), (c, "c")):
+        assert np.array_equal(got.cpu().numpy(), tr[name]), name
+    # two interleaved halves (what two ranks would compute) give the same values
+    half = [tuple(torch.empty((m // 2, 32), dtype=torch.uint8, device="cuda") for _ in range(3)) for _ in range(2)]
+    for k1 in range(2):
+        ctx.abc_evals_strided_device(pk, dz.data_ptr(), k1, 2, m // 2, *(t.data_ptr() for t in half[k1]))
+    ctx.synchronize()
+    assert torch.equal(half[0][0], a[0::2].contiguous()) and torch.equal(half[1][2], c[1::2].contiguous())
+    for v in (a, b, c):
+        ctx.ntt_device(v.data_ptr(), log_m, inverse=True)
+        ctx.ntt_device(v.data_ptr(), log_m, inverse=False, coset=True)
+    h = torch.empty((m, 32), dtype=torch.uint8, device="cuda")
+    ctx.h_pointwise_device(a.data_ptr(), b.data_ptr(), c.data_ptr(), m, log_m, h.data_ptr())
+    ctx.ntt_device(h.data_ptr(), log_m, inverse=True, coset=True)
+    ctx.synchronize()
+    assert np.array_equal(h.cpu().numpy(), tr["h"])
+    part = ctx.prove_partial_h(pk, dz.data_ptr(), 0, 1, h.data_ptr(), 0, m)
+    assert ctx.prove_assemble(pk, part, r, sr) == want
+    # two H blocks with the other four queries split in two as well
+    parts = np.stack([ctx.prove_partial_h(pk, dz.data_ptr(), k, 2, h[k * (m // 2):].data_ptr(), k * (m // 2), m // 2) for k in range(2)])
+    assert ctx.prove_assemble(pk, parts, r, sr) == want
+    bad = h.clone(); bad[5] = 0xFF
+    with pytest.raises(lib.B2g16Error):
+        ctx.prove_partial_h(pk, dz.data_ptr(), 0, 1, bad.data_ptr(), 0, m)
+    pk.free()

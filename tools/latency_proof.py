@@ -20,6 +20,7 @@ from b2g16 import codec, dist as bd, lib
 def main():
     workload = sys.argv[1] if len(sys.argv) > 1 else "porep-c2-32GiB"
     reps = int(sys.argv[2]) if len(sys.argv) > 2 else 3
+    mode = sys.argv[3] if len(sys.argv) > 3 else "msm"        # "msm": multiexps sharded, witness map repeated; "full": witness map sharded too
     rank, world, local = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)), int(os.environ.get("LOCAL_RANK", 0))
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
@@ -46,10 +47,16 @@ def main():
         if world > 1:
             dist.barrier()
     times, proof = [], None
+    peer = bd.PeerNtt(ctx, log_m) if (world > 1 and mode == "full") else None
     for _ in range(reps + 1):
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier(); e0.record()
-        p = bd.prove_sharded(ctx, pk, dz.data_ptr(), r, sr) if world > 1 else ctx.prove_device(pk, dz.data_ptr(), r, sr)
+        if world == 1:
+            p = ctx.prove_device(pk, dz.data_ptr(), r, sr)
+        elif peer is not None:
+            p = bd.prove_sharded_full(ctx, pk, peer, dz.data_ptr(), r, sr)
+        else:
+            p = bd.prove_sharded(ctx, pk, dz.data_ptr(), r, sr)
         e1.record(); barrier()
         ms = e0.elapsed_time(e1)
         if world > 1:
@@ -70,7 +77,10 @@ def main():
         print(json.dumps({"workload": workload, "describe": bench.WORKLOADS[workload][2], "log_m": log_m, "n_in": n_in, "n_cons": shape["n_cons"], "n_gpus": world,
                           "prove_s": min(times[1:]), "all_s": times, "first_s_includes_table_setup": times[0], "setup_s": setup_s, "proof_head": proof[:8].hex(),
                           "verified_natively": bool(ok), "perturbed_input_rejected": bool(rejected), "verify_s": verify_s,
-                          "mode": "five multiexps range-sharded over the ranks, witness map on every rank" if world > 1 else "single GPU"}), flush=True)
+                          "mode": "single GPU" if world == 1 else ("five multiexps range-sharded over the ranks, witness map sharded (fused peer-memory transforms)" if peer is not None
+                                                                     else "five multiexps range-sharded over the ranks, witness map on every rank")}), flush=True)
+    if peer is not None:
+        peer.close()
     pk.free(); ctx.close()
     if world > 1:
         dist.barrier(); dist.destroy_process_group()
