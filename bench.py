@@ -332,11 +332,24 @@ def run_b200(args):
             barrier(); e0.record(); p_s = bd.prove_sharded(ctx, pk, dz.data_ptr(), r, sr); e1.record(); barrier()
             strong.append(max_over_ranks(e0.elapsed_time(e1)))
             assert p_s == p_ref
+        full = []
+        if world in (2, 4, 8):
+            peer = bd.PeerNtt(ctx, log_m)
+            assert bd.prove_sharded_full(ctx, pk, peer, dz.data_ptr(), r, sr) == p_ref
+            for _ in range(3):
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                barrier(); e0.record(); p_f = bd.prove_sharded_full(ctx, pk, peer, dz.data_ptr(), r, sr); e1.record(); barrier()
+                full.append(max_over_ranks(e0.elapsed_time(e1)))
+                assert p_f == p_ref
+            peer.close()
         if rank == 0:
             assert p_ref == ctx.prove_device(pk, dz.data_ptr(), r, sr), "sharded proof differs from the single-GPU proof"
             line["one_proof_sharded"] = {"n_gpus": world, "prove_s": min(strong) / 1e3, "all_s": [t / 1e3 for t in strong], "scaling": "strong",
                                          "how": "every rank runs the witness map and reduces 1/N of each of the five queries (b2g16_prove_partial); all_gather of N x 576 B over NCCL; b2g16_prove_assemble",
-                                         "speedup_vs_1gpu_step": (ms / args.steps) / min(strong)}
+                                         "speedup_vs_1gpu_step": (ms / args.steps) / min(strong),
+                                         "witness_map_sharded_too": None if not full else {
+                                             "prove_s": min(full) / 1e3, "all_s": [t / 1e3 for t in full], "speedup_vs_1gpu_step": (ms / args.steps) / min(full),
+                                             "how": "rows k1 + N k2 of a, b, c per rank, seven transforms on the fused peer-memory path (b2g16.dist.PeerNtt), pointwise quotient, each rank's H block feeds its share of the H query (b2g16_prove_partial_h)"}}
     pk.free()
     del dz, hz
     if rank == 0 and not args.skip_standalone:

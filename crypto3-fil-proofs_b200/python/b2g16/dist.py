@@ -116,7 +116,9 @@ class PartitionScheduler:
     all partitions; d_assignment_for(k) returns the device pointer of partition k's witness on this rank (it is
     called only for partitions this rank takes part in)."""
 
-    def __init__(self, n_partitions, group=None):
+    def __init__(self, n_partitions, group=None, ctx=None, log_m=None):
+        """With ctx and log_m given, every sub-group also gets a PeerNtt so its proofs shard the witness map too
+        (prove_sharded_full); otherwise they repeat it on every rank (prove_sharded)."""
         self.world, self.rank = dist.get_world_size(group), dist.get_rank(group)
         self.n = n_partitions
         self.plan = partition_schedule(n_partitions, self.world)
@@ -125,6 +127,16 @@ class PartitionScheduler:
             if len(ranks) > 1 and tuple(ranks) not in self.groups:
                 self.groups[tuple(ranks)] = dist.new_group(ranks=ranks)        # every rank calls new_group for every group
         self.parent = group
+        self.peers = {}
+        if ctx is not None and log_m is not None:
+            for ranks, g in self.groups.items():
+                if self.rank in ranks and len(ranks) in (2, 4, 8) and log_m >= 2 * (len(ranks).bit_length() - 1):
+                    self.peers[ranks] = PeerNtt(ctx, log_m, group=g)
+
+    def close(self):
+        for p in self.peers.values():
+            p.close()
+        self.peers = {}
 
     def prove_all(self, ctx, pk, d_assignment_for, rs, ss):
         local = {}
@@ -133,6 +145,8 @@ class PartitionScheduler:
                 continue
             if len(ranks) == 1:
                 local[k] = ctx.prove_device(pk, d_assignment_for(k), rs[k], ss[k])
+            elif tuple(ranks) in self.peers:
+                local[k] = prove_sharded_full(ctx, pk, self.peers[tuple(ranks)], d_assignment_for(k), rs[k], ss[k], group=self.groups[tuple(ranks)])
             else:
                 local[k] = prove_sharded(ctx, pk, d_assignment_for(k), rs[k], ss[k], group=self.groups[tuple(ranks)])
         # owner of partition k for the gather = first rank of its group

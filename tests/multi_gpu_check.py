@@ -106,7 +106,7 @@ def main():
     assert bd.prove_sharded(ctx, pk, dz0.data_ptr(), rs[0], ss[0]) == multi[:192], ("prove_sharded", rank)
     checks += 1
     # scheduled multi-proof: full waves one partition per GPU, the remainder spread over sub-groups
-    sched = bd.PartitionScheduler(n_part)
+    sched = bd.PartitionScheduler(n_part, ctx=ctx, log_m=s.log_m)          # remainder proofs shard the witness map too
     dzs = {}
 
     def d_for(k):
@@ -117,6 +117,7 @@ def main():
         n3 = world + world // 2                                       # remainder world/2 -> groups of 2
         sched3 = bd.PartitionScheduler(n3)
         assert sched3.prove_all(ctx, pk, d_for, rs, ss) == multi[:192 * n3], ("scheduled multi-proof, groups of 2", rank)
+    sched.close()
     checks += 1
     # ... and with the witness map sharded too (transforms on the fused peer-memory path)
     pn = bd.PeerNtt(ctx, s.log_m)

@@ -33,7 +33,7 @@ def main():
     t0 = time.perf_counter()
     pk, vk = ctx.pk_generate_synth(log_m, n_in, n_free, seed, toxic, want_vk=True)
     nv = pk.shape()["n_vars"]
-    sched = bd.PartitionScheduler(n_part)
+    sched = bd.PartitionScheduler(n_part, ctx=ctx, log_m=log_m)
     heads, dzs = {}, {}
     for k in range(n_part):
         heads[k] = codec.random_fr(1 + n_in + n_free, np.random.Generator(np.random.PCG64(5000 + k)))
@@ -72,6 +72,7 @@ def main():
                           "prove_all_s": min(times), "all_s": times, "setup_s": setup_s,
                           "schedule": [[k, ranks] for k, ranks in sched.plan], "batch_verified_natively": bool(ok), "perturbed_input_rejected": bool(rejected),
                           "verify_batch_s": verify_s}), flush=True)
+    sched.close()
     pk.free(); ctx.close()
     dist.barrier(); dist.destroy_process_group()
 
