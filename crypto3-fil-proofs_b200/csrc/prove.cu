@@ -190,19 +190,6 @@ static Fr host_fr_from_bytes(const uint8_t* b32, bool* ok) {
     if (Fr::geq_p(c)) { *ok = false; return Fr::zero(); }
     return Fr::from_canonical(c);
 }
-template <class F> static Xyzz<F> host_scalar_mul(const Xyzz<F>& p, const Fr& k_mont) {
-    uint32_t k[8]; k_mont.to_canonical(k);
-    Xyzz<F> table[16];                                  // 4-bit fixed window
-    table[0] = Xyzz<F>::identity();
-    for (int i = 1; i < 16; ++i) { table[i] = table[i - 1]; table[i].add(p); }
-    Xyzz<F> acc = Xyzz<F>::identity();
-    for (int nib = 63; nib >= 0; --nib) {
-        for (int d = 0; d < 4; ++d) acc = acc.dbl();
-        uint32_t v = (k[nib >> 3] >> (4 * (nib & 7))) & 15u;
-        if (v) acc.add(table[v]);
-    }
-    return acc;
-}
 static Fq host_fq_from_bytes(const uint8_t* b48) { uint32_t c[12]; memcpy(c, b48, 48); return Fq::from_canonical(c); }
 static void host_fq_to_bytes(const Fq& f, uint8_t* b48) { uint32_t c[12]; f.to_canonical(c); memcpy(b48, c, 48); }
 static G1Affine host_g1_from_bytes(const uint8_t* b) { return {host_fq_from_bytes(b), host_fq_from_bytes(b + 48)}; }
@@ -213,24 +200,7 @@ static void host_g1_to_bytes(const G1Affine& p, uint8_t* b) { host_fq_to_bytes(p
 static void host_g2_to_bytes(const G2Affine& p, uint8_t* b) {
     host_fq_to_bytes(p.x.c0, b); host_fq_to_bytes(p.x.c1, b + 48); host_fq_to_bytes(p.y.c0, b + 96); host_fq_to_bytes(p.y.c1, b + 144);
 }
-// zcash-style compressed encoding: big-endian x, bit7 compressed,
-// bit6 infinity, bit5 set iff y is the lexicographically larger root.
-static void put_be48(const Fq& x, uint8_t* o) { uint8_t le[48]; host_fq_to_bytes(x, le); for (int i = 0; i < 48; ++i) o[i] = le[47 - i]; }
-static bool fq_larger_half(const Fq& y) {
-    uint32_t a[12], b[12]; y.to_canonical(a); y.neg().to_canonical(b);
-    for (int i = 11; i >= 0; --i) if (a[i] != b[i]) return a[i] > b[i];
-    return false;
-}
-static void compress_g1(const G1Affine& p, uint8_t* o) {
-    if (p.is_identity()) { memset(o, 0, 48); o[0] = 0xC0; return; }
-    put_be48(p.x, o); o[0] |= 0x80; if (fq_larger_half(p.y)) o[0] |= 0x20;
-}
-static void compress_g2(const G2Affine& p, uint8_t* o) {
-    if (p.is_identity()) { memset(o, 0, 96); o[0] = 0xC0; return; }
-    put_be48(p.x.c1, o); put_be48(p.x.c0, o + 48); o[0] |= 0x80;
-    bool larger = p.y.c1.is_zero() ? fq_larger_half(p.y.c0) : fq_larger_half(p.y.c1);
-    if (larger) o[0] |= 0x20;
-}
+// (point compression of the 192-byte proof: host_bls.hpp, shared with the verifier)
 
 // ------------------------------------------------------------------------------ key load
 static void free_csr(DevCsr& m) { cudaFree(m.row_ptr); cudaFree(m.col); cudaFree(m.val); m = DevCsr(); }
