@@ -106,6 +106,10 @@ void h_from_abc_dev(Ctx* c, Fr* d_a, Fr* d_b, Fr* d_c, int log_m, uint32_t* d_h_
 // device scalars; the affine result is written to d_out_bytes in the ABI encoding (96 / 192 B).
 void msm_g1_dev(Ctx* c, const G1Affine* d_bases, const uint32_t* d_scalars, size_t n, uint8_t* d_out_bytes, cudaStream_t st, int window_bits);
 void msm_g2_dev(Ctx* c, const G2Affine* d_bases, const uint32_t* d_scalars, size_t n, uint8_t* d_out_bytes, cudaStream_t st, int window_bits);
+// same reduction, but the (at most 32) window sums are left in d_win for the caller to combine: result =
+// sum_w 2^(c_bits w) d_win[w]; n_windows = 0 for the empty sum
+void msm_g1_windows_dev(Ctx* c, const G1Affine* d_bases, const uint32_t* d_scalars, size_t n, G1Xyzz* d_win, int* c_bits, int* n_windows, cudaStream_t st);
+void msm_g2_windows_dev(Ctx* c, const G2Affine* d_bases, const uint32_t* d_scalars, size_t n, G2Xyzz* d_win, int* c_bits, int* n_windows, cudaStream_t st);
 void gen_mul_g1_dev(Ctx* c, const uint32_t* d_scalars, size_t n, G1Affine* d_out);
 void gen_mul_g2_dev(Ctx* c, const uint32_t* d_scalars, size_t n, G2Affine* d_out);
 void sum_g1_dev(Ctx* c, const G1Affine* d_pts, size_t n, uint8_t* d_out_bytes);

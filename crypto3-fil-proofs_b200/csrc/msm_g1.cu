@@ -10,6 +10,11 @@ static const uint32_t G1_GEN_Y[12] = {0x46c5e7e1u, 0x0caa2329u, 0xa2888ae4u, 0xd
 void msm_g1_dev(Ctx* c, const G1Affine* d_bases, const uint32_t* d_scalars, size_t n, uint8_t* d_out_bytes, cudaStream_t st, int window_bits) {
     msm_run<Fq>(c, d_bases, d_scalars, n, d_out_bytes, st, window_bits);
 }
+void msm_g1_windows_dev(Ctx* c, const G1Affine* d_bases, const uint32_t* d_scalars, size_t n, G1Xyzz* d_win /*32*/, int* c_bits, int* n_windows, cudaStream_t st) {
+    MsmPlan plan{0, 0};
+    msm_run<Fq>(c, d_bases, d_scalars, n, nullptr, st, 0, d_win, &plan);
+    *c_bits = plan.c; *n_windows = plan.W;
+}
 void gen_mul_g1_dev(Ctx* c, const uint32_t* d_scalars, size_t n, G1Affine* d_out) {
     if (!n) return;
     G1Affine gen{Fq::from_canonical(G1_GEN_X), Fq::from_canonical(G1_GEN_Y)};

@@ -13,6 +13,11 @@ static const uint32_t G2_GEN[4][12] = {
 void msm_g2_dev(Ctx* c, const G2Affine* d_bases, const uint32_t* d_scalars, size_t n, uint8_t* d_out_bytes, cudaStream_t st, int window_bits) {
     msm_run<Fq2>(c, d_bases, d_scalars, n, d_out_bytes, st, window_bits);
 }
+void msm_g2_windows_dev(Ctx* c, const G2Affine* d_bases, const uint32_t* d_scalars, size_t n, G2Xyzz* d_win /*32*/, int* c_bits, int* n_windows, cudaStream_t st) {
+    MsmPlan plan{0, 0};
+    msm_run<Fq2>(c, d_bases, d_scalars, n, nullptr, st, 0, d_win, &plan);
+    *c_bits = plan.c; *n_windows = plan.W;
+}
 void gen_mul_g2_dev(Ctx* c, const uint32_t* d_scalars, size_t n, G2Affine* d_out) {
     if (!n) return;
     G2Affine gen{{Fq::from_canonical(G2_GEN[0]), Fq::from_canonical(G2_GEN[1])}, {Fq::from_canonical(G2_GEN[2]), Fq::from_canonical(G2_GEN[3])}};

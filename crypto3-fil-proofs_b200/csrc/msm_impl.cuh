@@ -478,10 +478,19 @@ static void launch_accumulate(Ctx* ctx, cudaStream_t st, size_t max_segs, const 
 #undef B2_ACC
 }
 
+// d_win_out == nullptr: the affine result goes to d_out_bytes (Horner over the windows by one device thread).
+// d_win_out != nullptr: the W window sums are copied there instead and *plan_out = {c, W}; the caller combines
+// them (the prover does it on the host: 240 dependent doublings are 3 ms for a lone GPU thread and 0.3 ms
+// for a CPU core).  W = 0 means the empty sum.
+struct MsmPlan { int c, W; };
 template <class F>
-void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size_t n, uint8_t* d_out_bytes, cudaStream_t st, int window_bits) {
+void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size_t n, uint8_t* d_out_bytes, cudaStream_t st, int window_bits,
+             Xyzz<F>* d_win_out = nullptr, MsmPlan* plan_out = nullptr) {
     constexpr int OUT_BYTES = (int)sizeof(Affine<F>);
-    if (n == 0) { B2_CUDA(cudaMemsetAsync(d_out_bytes, 0, OUT_BYTES, st)); return; }
+    if (n == 0) {
+        if (d_win_out) { plan_out->c = 0; plan_out->W = 0; return; }
+        B2_CUDA(cudaMemsetAsync(d_out_bytes, 0, OUT_BYTES, st)); return;
+    }
     B2_REQUIRE(n < ((size_t)1 << 31), B2G16_E_INVALID_ARG, "msm: at most 2^31-1 points per call");
     int c = window_bits ? window_bits : (ctx->msm_window_override ? ctx->msm_window_override : msm_pick_window(n));
     B2_REQUIRE(c >= 8 && c <= 23, B2G16_E_INVALID_ARG, "msm: window bits must be in [8, 23]");
@@ -581,7 +590,13 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
         msm_window_sum_kernel<F><<<W, 32, 0, st>>>(partial.get(), T, red_a[0].get()); ctx->launches++;
         win = red_a[0].get();
     }
-    msm_final_kernel<F><<<1, 32, 0, st>>>(win, c, W, d_out_bytes); ctx->launches++;
+    if (d_win_out) {
+        B2_REQUIRE(W <= 32, B2G16_E_INTERNAL, "msm: window count");
+        B2_CUDA(cudaMemcpyAsync(d_win_out, win, (size_t)W * sizeof(Xyzz<F>), cudaMemcpyDeviceToDevice, st));
+        plan_out->c = c; plan_out->W = W;
+    } else {
+        msm_final_kernel<F><<<1, 32, 0, st>>>(win, c, W, d_out_bytes); ctx->launches++;
+    }
     mark(5);
     B2_CUDA(cudaGetLastError());
     if (timed) {

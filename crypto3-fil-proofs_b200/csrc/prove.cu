@@ -10,6 +10,7 @@
 //           -> 192-byte compressed proof (F/constants.hpp:93 SINGLE_PARTITION_PROOF_LEN)
 // The key layout mirrors scheme_params (S/core/crypto/scheme_params.hpp:38-67), dense.
 #include <cstring>
+#include <thread>
 #include <vector>
 #include "msm_impl.cuh"
 #include "api_util.cuh"
@@ -258,6 +259,22 @@ template <class A> static A* upload_points(Ctx* c, const uint8_t* bytes, size_t 
 
 // ---------------------------------------------------------------------------- the prover
 struct MsmOut { uint8_t a[96], b1[96], l[96], h[96], b2[192]; };
+// window sums of the five multiexps as the device leaves them (msm_*_windows_dev); combined on the host
+struct WinBuf { G1Xyzz a[32], b1[32], l[32], h[32]; G2Xyzz b2[32]; };
+// sum_w 2^(c w) win[w] by Horner in the host's 64-bit arithmetic.  Device XYZZ accumulators (12 x u32 Montgomery
+// limbs per coordinate) and host_bls.hpp's Pt (6 x u64) are the same bytes.
+template <class HF, class DX> static b2h::Aff<HF> host_horner(const DX* win, int c, int W) {
+    static_assert(sizeof(DX) == sizeof(b2h::Pt<HF>), "device and host accumulator layouts differ");
+    if (W == 0) return b2h::Aff<HF>::identity();
+    b2h::Pt<HF> acc, t;
+    memcpy(&acc, &win[W - 1], sizeof acc);
+    for (int w = W - 2; w >= 0; --w) {
+        for (int k = 0; k < c; ++k) acc = acc.dbl();
+        memcpy(&t, &win[w], sizeof t);
+        acc = acc.add(t);
+    }
+    return acc.affine();
+}
 
 // abc_host: optional {a32, b32, c32} host evaluations supplied by the caller's synthesis (b2g16_prove_abc);
 // otherwise a, b, c come from the key's CSR matrices.
@@ -287,8 +304,10 @@ static void prove_one(Ctx* c, const b2g16_pk* pk, const uint8_t* d_z_canon, cons
     const bool ext_h = d_h_slice != nullptr;
     DevBuf<Fr> z(ext_h ? 0 : nv, st), a(ext_h ? 0 : m, st), b(ext_h ? 0 : m, st), cc(ext_h ? 0 : m, st);
     DevBuf<uint32_t> h(ext_h ? 0 : m * 8, st);
-    DevBuf<uint8_t> d_out(sizeof(MsmOut), st);
+    DevBuf<uint8_t> d_win(sizeof(WinBuf), st);
     MsmOut out;
+    static thread_local WinBuf win;                      // 36 KB: not on the stack
+    int cb[5] = {0, 0, 0, 0, 0}, nw[5] = {0, 0, 0, 0, 0};
     B2_CUDA(cudaEventRecord(ev[0], st));
     if (ext_h) scalars_check_dev(c, d_z_canon, nv, bad.ptr());
     else fr_from_bytes_dev(c, d_z_canon, z.get(), nv, bad.ptr());
@@ -321,25 +340,25 @@ static void prove_one(Ctx* c, const b2g16_pk* pk, const uint8_t* d_z_canon, cons
     B2_CUDA(cudaEventRecord(c->ev_fork, st));
     for (int i = 0; i < 4; ++i) B2_CUDA(cudaStreamWaitEvent(c->aux[i], c->ev_fork, 0));
     const uint32_t* zc = reinterpret_cast<const uint32_t*>(d_z_canon);
-    uint8_t* o = d_out.get();
+    WinBuf* dw = reinterpret_cast<WinBuf*>(d_win.get());
     // above 2^24 the witness MSMs run one after the other on the main stream: each needs ~9 GB of sort
     // scratch at 2^27 and the integer pipe serialises them anyway; below, they overlap the NTT chain
     const bool serial = (int)pk->log_m > c->serial_above_log;
     cudaStream_t s_b2 = serial ? st : c->aux[0], s_a = serial ? st : c->aux[1], s_b1 = serial ? st : c->aux[2], s_l = serial ? st : c->aux[3];
-    msm_g2_dev(c, pk->b_g2 + lo_of(nv), zc + 8 * lo_of(nv), cnt_of(nv), o + offsetof(MsmOut, b2), s_b2, 0);
-    msm_g1_dev(c, pk->a + lo_of(nv), zc + 8 * lo_of(nv), cnt_of(nv), o + offsetof(MsmOut, a), s_a, 0);
-    msm_g1_dev(c, pk->b_g1 + lo_of(nv), zc + 8 * lo_of(nv), cnt_of(nv), o + offsetof(MsmOut, b1), s_b1, 0);
-    msm_g1_dev(c, pk->l + lo_of(pk->n_aux), zc + 8 * (1 + pk->n_in + lo_of(pk->n_aux)), cnt_of(pk->n_aux), o + offsetof(MsmOut, l), s_l, 0);
+    msm_g2_windows_dev(c, pk->b_g2 + lo_of(nv), zc + 8 * lo_of(nv), cnt_of(nv), dw->b2, &cb[4], &nw[4], s_b2);
+    msm_g1_windows_dev(c, pk->a + lo_of(nv), zc + 8 * lo_of(nv), cnt_of(nv), dw->a, &cb[0], &nw[0], s_a);
+    msm_g1_windows_dev(c, pk->b_g1 + lo_of(nv), zc + 8 * lo_of(nv), cnt_of(nv), dw->b1, &cb[1], &nw[1], s_b1);
+    msm_g1_windows_dev(c, pk->l + lo_of(pk->n_aux), zc + 8 * (1 + pk->n_in + lo_of(pk->n_aux)), cnt_of(pk->n_aux), dw->l, &cb[2], &nw[2], s_l);
     if (!ext_h) h_from_abc_dev(c, a.get(), b.get(), cc.get(), (int)pk->log_m, h.get(), false, nullptr);
     B2_CUDA(cudaEventRecord(ev[3], st));
     if (ext_h) {
         const uint64_t hi = h_first + h_count < m - 1 ? h_first + h_count : m - 1;       // h_{m-1} = 0 has no base
         const uint64_t cnt = hi > h_first ? hi - h_first : 0;
-        msm_g1_dev(c, pk->h + h_first, reinterpret_cast<const uint32_t*>(d_h_slice), cnt, o + offsetof(MsmOut, h), st, 0);
+        msm_g1_windows_dev(c, pk->h + h_first, reinterpret_cast<const uint32_t*>(d_h_slice), cnt, dw->h, &cb[3], &nw[3], st);
     } else
-        msm_g1_dev(c, pk->h + lo_of(m - 1), h.get() + 8 * lo_of(m - 1), cnt_of(m - 1), o + offsetof(MsmOut, h), st, 0);
+        msm_g1_windows_dev(c, pk->h + lo_of(m - 1), h.get() + 8 * lo_of(m - 1), cnt_of(m - 1), dw->h, &cb[3], &nw[3], st);
     for (int i = 0; i < 4; ++i) { B2_CUDA(cudaEventRecord(c->ev_join[i], c->aux[i])); B2_CUDA(cudaStreamWaitEvent(st, c->ev_join[i], 0)); }
-    B2_CUDA(cudaMemcpyAsync(&out, o, sizeof(MsmOut), cudaMemcpyDeviceToHost, st));
+    B2_CUDA(cudaMemcpyAsync(&win, dw, sizeof(WinBuf), cudaMemcpyDeviceToHost, st));
     if (tr && tr->h && !ext_h) B2_CUDA(cudaMemcpyAsync(tr->h, h.get(), m * 32, cudaMemcpyDeviceToHost, st));
     B2_CUDA(cudaEventRecord(ev[4], st));
     bad.check("assignment");                              // synchronises the stream
@@ -348,6 +367,19 @@ static void prove_one(Ctx* c, const b2g16_pk* pk, const uint8_t* d_z_canon, cons
         for (int i = 0; i < 4; ++i) cudaEventElapsedTime(&tr->stage_ms[i], ev[i], ev[i + 1]);   // ingest, abc, ntt/h, msm_h + join of the rest
     }
     for (auto& e : ev) cudaEventDestroy(e);
+    // Horner over the windows of each multiexp, on the host (the stream is idle: bad.check synchronised it);
+    // the five combinations are independent: one thread each, the G2 one (3x the work) on this thread
+    {
+        const WinBuf* w = &win;
+        MsmOut* op = &out;
+        std::thread th[4] = {
+            std::thread([=] { b2h::g1_to_abi(host_horner<b2h::Fq>(w->a, cb[0], nw[0]), op->a); }),
+            std::thread([=] { b2h::g1_to_abi(host_horner<b2h::Fq>(w->b1, cb[1], nw[1]), op->b1); }),
+            std::thread([=] { b2h::g1_to_abi(host_horner<b2h::Fq>(w->l, cb[2], nw[2]), op->l); }),
+            std::thread([=] { b2h::g1_to_abi(host_horner<b2h::Fq>(w->h, cb[3], nw[3]), op->h); })};
+        b2h::g2_to_abi(host_horner<b2h::Fq2>(w->b2, cb[4], nw[4]), op->b2);
+        for (auto& t : th) t.join();
+    }
     if (partial_out) { *partial_out = out; return; }
     assemble_proof(pk, out, r32, s32, proof_out, tr);
 }
