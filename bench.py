@@ -158,6 +158,11 @@ def cpu_prove_sample(workload, sample_log_m, steps=1, warmup=0, seed=2026):
     from oracle import coracle
     from b2g16 import synth
     coracle.build()
+    # all host cores, whatever the launcher exported (torchrun sets OMP_NUM_THREADS=1 for its workers)
+    try:
+        coracle.set_threads(len(os.sched_getaffinity(0)))
+    except AttributeError:
+        coracle.set_threads(os.cpu_count() or 1)
     log_m = WORKLOADS[workload][0]
     n_in = n_in_of(workload)
     sample_log_m = min(sample_log_m, log_m)
