@@ -19,6 +19,7 @@
 // Results are canonical affine points, hence bit-exact whatever the summation order.
 #pragma once
 #include "common.cuh"
+#include <cstdlib>
 #include "msm_digits.cuh"
 
 namespace b2 {
@@ -430,11 +431,14 @@ template <class F> __global__ void __launch_bounds__(128) gen_mul_kernel(const A
 // local as buckets multiply -- 16 bits up to 2^22 points, 20 bits from 2^23.  Standalone, 17 bits is 1.5 % faster
 // for 2^20 .. 2^23 points (profiles/r01_window_sweep2_g{1,2}.jsonl), but inside a proof it moves the G2 multiexp
 // onto the chunked kernel, whose few long CTAs co-schedule badly with the other four multiexps running on
-// sibling streams (2^22 proof: 0.261 s against 0.241 s), so the proof-friendly choice stays.
-inline int msm_pick_window(size_t n) {
+// sibling streams (2^22 proof: 0.261 s against 0.241 s); 17 bits for G1 alone (B2G16_G1_C17=1) makes each
+// accumulate launch 1.6 ms shorter and the proof 7 ms longer (0.248 s).  The proof-friendly choice stays.
+inline bool g1_17bit_windows() { static const bool on = getenv("B2G16_G1_C17") != nullptr; return on; }
+inline int msm_pick_window(size_t n, bool g2 = false) {
     int lg = 0;
     while (((size_t)1 << (lg + 1)) <= n) ++lg;
     if (lg >= 23) return 20;
+    if (!g2 && lg >= 20 && g1_17bit_windows()) return 17;          // experiment knob B2G16_G1_C17 (see above)
     int c = lg - 4;
     if (c < 8) c = 8;
     if (c > 16) c = 16;
@@ -492,7 +496,7 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
         B2_CUDA(cudaMemsetAsync(d_out_bytes, 0, OUT_BYTES, st)); return;
     }
     B2_REQUIRE(n < ((size_t)1 << 31), B2G16_E_INVALID_ARG, "msm: at most 2^31-1 points per call");
-    int c = window_bits ? window_bits : (ctx->msm_window_override ? ctx->msm_window_override : msm_pick_window(n));
+    int c = window_bits ? window_bits : (ctx->msm_window_override ? ctx->msm_window_override : msm_pick_window(n, sizeof(F) > 48));
     B2_REQUIRE(c >= 8 && c <= 23, B2G16_E_INVALID_ARG, "msm: window bits must be in [8, 23]");
     const int W = msm_windows(c);
     const uint32_t B = 1u << (c - 1);
