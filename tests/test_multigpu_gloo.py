@@ -40,7 +40,27 @@ def _worker(rank, world, port, q):
         local = {k: bytes([k + 1]) * 192 for k in bd.my_partitions(5, rank, world)}
         multi = bd.gather_proofs(local, 5)
         ok_proofs = multi == b"".join(bytes([k + 1]) * 192 for k in range(5))
-        q.put((rank, ok_msm, ok_proofs, (first, last)))
+        # scheduled multi-proof: 5 partitions on 2 ranks = two full waves + one proof spread over both ranks.
+        # The device calls are stubbed (a "pointer" is the partition index); what is under test is the sub-group
+        # creation, who proves what, and the order of the gathered 192-byte records.
+
+        class StubCtx:
+            def prove_device(self, pk, ptr, r, s):
+                return bytes([ptr + 1]) * 192
+
+            def prove_partial(self, pk, ptr, part, parts):
+                out = np.zeros(576, dtype=np.uint8)
+                out[0], out[1], out[2] = ptr, part, parts
+                return out
+
+            def prove_assemble(self, pk, partials, r, s):
+                p = np.asarray(partials).reshape(-1, 576)
+                assert p.shape[0] == p[0, 2] and sorted(p[:, 1].tolist()) == list(range(p.shape[0])) and len(set(p[:, 0].tolist())) == 1
+                return bytes([int(p[0, 0]) + 1]) * 192
+        sched = bd.PartitionScheduler(5)
+        multi2 = sched.prove_all(StubCtx(), None, lambda k: k, [None] * 5, [None] * 5)
+        ok_sched = multi2 == b"".join(bytes([k + 1]) * 192 for k in range(5)) and [ranks for _, ranks in sched.plan] == [[0], [1], [0], [1], [0, 1]]
+        q.put((rank, ok_msm, ok_proofs and ok_sched, (first, last)))
     finally:
         dist.destroy_process_group()
 
