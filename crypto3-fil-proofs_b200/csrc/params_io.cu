@@ -147,4 +147,55 @@ int b2g16_params_vk_bytes(const b2g16_params* p, uint8_t* vk_out, size_t vk_byte
     return B2G16_OK;
 }
 
+// Density-filtered queries (bellman generator: points at infinity are dropped from a / b_g1 / b_g2;
+// its prover skips them through the a_aux / b_input / b_aux density bitmaps) <-> the dense layout of
+// scheme_params.hpp:46-66 that b2g16_pk_view takes.  A column's polynomial is zero exactly when the
+// variable occurs in no row, so the bitmap is the column occupancy of the matrix.
+int b2g16_csr_density(const b2g16_csr* m, uint64_t n_vars, uint8_t* density_out, uint64_t* count_out) {
+    if (!m || !density_out || (m->nnz && !m->col)) return B2G16_E_INVALID_ARG;
+    memset(density_out, 0, n_vars);
+    for (uint64_t k = 0; k < m->nnz; ++k) {
+        if (m->col[k] >= n_vars) return B2G16_E_INVALID_ARG;
+        density_out[m->col[k]] = 1;
+    }
+    if (count_out) {
+        uint64_t c = 0;
+        for (uint64_t j = 0; j < n_vars; ++j) c += density_out[j];
+        *count_out = c;
+    }
+    return B2G16_OK;
+}
+
+int b2g16_query_expand(const uint8_t* filtered, uint64_t n_filtered, const uint8_t* density, uint64_t n_vars, size_t point_bytes,
+                       uint8_t* dense_out) {
+    if ((!filtered && n_filtered) || !density || !dense_out || (point_bytes != 96 && point_bytes != 192)) return B2G16_E_INVALID_ARG;
+    uint64_t set = 0;
+    for (uint64_t j = 0; j < n_vars; ++j) set += density[j] != 0;
+    if (set != n_filtered) return B2G16_E_INVALID_ARG;          // file and constraint system disagree: refuse before writing
+    uint64_t k = 0;
+    for (uint64_t j = 0; j < n_vars; ++j) {
+        if (density[j]) memcpy(dense_out + j * point_bytes, filtered + (k++) * point_bytes, point_bytes);
+        else memset(dense_out + j * point_bytes, 0, point_bytes);
+    }
+    return B2G16_OK;
+}
+
+int b2g16_query_filter(const uint8_t* dense, uint64_t n_vars, size_t point_bytes, uint8_t* filtered_out, uint8_t* density_out,
+                       uint64_t* count_out) {
+    if ((!dense && n_vars) || (point_bytes != 96 && point_bytes != 192)) return B2G16_E_INVALID_ARG;
+    uint64_t k = 0;
+    for (uint64_t j = 0; j < n_vars; ++j) {
+        const uint8_t* p = dense + j * point_bytes;
+        uint8_t any = 0;
+        for (size_t b = 0; b < point_bytes; ++b) any |= p[b];
+        if (density_out) density_out[j] = any != 0;
+        if (any) {
+            if (filtered_out) memcpy(filtered_out + k * point_bytes, p, point_bytes);
+            ++k;
+        }
+    }
+    if (count_out) *count_out = k;
+    return B2G16_OK;
+}
+
 }  // extern "C"

@@ -85,6 +85,39 @@ def params_read(path):
     return out
 
 
+def csr_density(col, n_vars):
+    """b2g16_csr_density: bitmap (uint8, n_vars) of the variables that occur in a matrix given its CSR column indices."""
+    col = np.ascontiguousarray(col, dtype=np.uint32)
+    m = Csr(0, col.shape[0], None, _p(col), None)
+    out, cnt = np.zeros(n_vars, np.uint8), C.c_uint64()
+    rc = load().b2g16_csr_density(C.byref(m), C.c_uint64(n_vars), _p(out), C.byref(cnt))
+    if rc != 0:
+        raise B2g16Error(rc, "b2g16_csr_density: column index out of range")
+    return out, int(cnt.value)
+
+
+def query_expand(filtered, density, point_bytes):
+    """b2g16_query_expand: bellman-style density-filtered query -> dense (n_vars, point_bytes), identity where density is 0."""
+    filtered, density = _u8(filtered, point_bytes), _u8(density)
+    out = np.empty((density.shape[0], point_bytes), np.uint8)
+    rc = load().b2g16_query_expand(_p(filtered), C.c_uint64(filtered.shape[0]), _p(density), C.c_uint64(density.shape[0]),
+                                   C.c_size_t(point_bytes), _p(out))
+    if rc != 0:
+        raise B2g16Error(rc, "b2g16_query_expand: %d points for a bitmap with %d set" % (filtered.shape[0], int(np.count_nonzero(density))))
+    return out
+
+
+def query_filter(dense, point_bytes):
+    """b2g16_query_filter: dense query -> (filtered points, density bitmap)."""
+    dense = _u8(dense, point_bytes)
+    n, cnt = dense.shape[0], C.c_uint64()
+    dens, filt = np.zeros(n, np.uint8), np.empty((n, point_bytes), np.uint8)
+    rc = load().b2g16_query_filter(_p(dense), C.c_uint64(n), C.c_size_t(point_bytes), _p(filt), _p(dens), C.byref(cnt))
+    if rc != 0:
+        raise B2g16Error(rc, "b2g16_query_filter")
+    return filt[: int(cnt.value)].copy(), dens
+
+
 def proof_decode(proof):
     a, b, c = np.zeros(96, np.uint8), np.zeros(192, np.uint8), np.zeros(96, np.uint8)
     rc = load().b2g16_proof_decode(_p(_u8(np.frombuffer(bytes(proof), dtype=np.uint8))), _p(a), _p(b), _p(c))

@@ -245,6 +245,22 @@ int b2g16_params_free(b2g16_params*);
 int b2g16_params_write(const char* path, const b2g16_params*);
 /* vk block in the b2g16_vk_prepare layout; vk_bytes must be 672 + 96 * n_ic */
 int b2g16_params_vk_bytes(const b2g16_params*, uint8_t* vk_out, size_t vk_bytes);
+/* bellman / bellperson parameter files hold the a, b_g1 and b_g2 queries with the points at infinity
+ * filtered out (a variable that appears in no row of A, resp. B, has a zero polynomial), and their
+ * prover walks them with the density bitmaps it records during synthesis.  b2g16_pk_view wants the
+ * dense crypto3 layout, so a caller holding such a file derives the bitmap from the constraint
+ * system it loads anyway and expands:
+ *   b2g16_csr_density : density[j] = 1 iff column j (variable j of z) occurs in the matrix; *count_out = popcount
+ *   b2g16_query_expand: dense[j] = next filtered point if density[j] else identity (zero bytes);
+ *                       B2G16_E_INVALID_ARG unless n_filtered equals the number of set entries
+ *   b2g16_query_filter: the inverse (drops all-zero points), for writing bellman-style files;
+ *                       filtered_out may be NULL to count only
+ * point_bytes = 96 (G1) or 192 (G2).  Host-only. */
+int b2g16_csr_density(const b2g16_csr* m, uint64_t n_vars, uint8_t* density_out, uint64_t* count_out);
+int b2g16_query_expand(const uint8_t* filtered, uint64_t n_filtered, const uint8_t* density, uint64_t n_vars, size_t point_bytes,
+                       uint8_t* dense_out);
+int b2g16_query_filter(const uint8_t* dense, uint64_t n_vars, size_t point_bytes, uint8_t* filtered_out, uint8_t* density_out,
+                       uint64_t* count_out);
 
 /* ---- synthetic-instance support (bench/test): evaluate one layer of a forward-built R1CS on
  *      the device: for rows [row0,row1): z[out_base + i] = (A_i . z) * (B_i . z).  d_z canonical. */

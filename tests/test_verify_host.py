@@ -136,3 +136,37 @@ def test_params_file_layout_and_round_trip(tmp_path):
         lib.params_read(path)
     with pytest.raises(lib.B2g16Error):
         lib.params_read(str(tmp_path / "missing.params"))
+
+
+def test_density_filtered_queries():
+    """bellman-style files keep a / b_g1 / b_g2 without their points at infinity; the bitmap that puts them
+    back is the column occupancy of A (resp. B).  Pinned on the golden key: a query point is the identity
+    exactly where the matrix has no entry for that variable."""
+    from b2g16 import synth
+    g = util.golden("groth16_m4")
+    s = synth.SynthR1cs(int(g["log_m"]), int(g["n_in"]), int(g["seed"]), n_free=int(g["n_free"]))
+    n_vars = g["a"].shape[0]
+    for mat, names in ((s.A, (("a", 96),)), (s.B, (("b_g1", 96), ("b_g2", 192)))):
+        dens, cnt = lib.csr_density(mat[1], n_vars)
+        assert cnt == int(dens.sum())
+        for n, w in names:
+            assert np.array_equal(dens, g[n].any(axis=1).astype(np.uint8)), n
+            filt, dens2 = lib.query_filter(g[n], w)
+            assert np.array_equal(dens2, dens) and filt.shape == (cnt, w)
+            assert np.array_equal(filt, g[n][dens.astype(bool)])
+            assert np.array_equal(lib.query_expand(filt, dens, w), g[n])
+            with pytest.raises(lib.B2g16Error):
+                lib.query_expand(filt[:-1], dens, w)                         # file and constraint system disagree
+    # empty matrix / nothing filtered / everything filtered
+    dens, cnt = lib.csr_density(np.zeros(0, np.uint32), 5)
+    assert cnt == 0 and not dens.any()
+    assert not lib.query_expand(np.zeros((0, 96), np.uint8), dens, 96).any()
+    full = np.arange(3 * 192, dtype=np.uint32).astype(np.uint8).reshape(3, 192) | 1
+    filt, d = lib.query_filter(full, 192)
+    assert d.all() and np.array_equal(filt, full)
+    with pytest.raises(lib.B2g16Error):
+        lib.csr_density(np.array([7], np.uint32), 5)                         # column out of range
+    import ctypes as C
+    ones, out = np.ones(3, np.uint8), np.zeros(3 * 192, np.uint8)
+    rc = lib.load().b2g16_query_expand(lib._p(full), C.c_uint64(3), lib._p(ones), C.c_uint64(3), C.c_size_t(100), lib._p(out))
+    assert rc == -1                                                          # not a point size
