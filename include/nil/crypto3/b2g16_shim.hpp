@@ -268,6 +268,77 @@ template <class CurveType> struct r1cs_gg_ppzksnark {
             c.check(b2g16_pk_load(c.get(), &v, &pk));
             return proving_key_type(pk, 1 + cs.n_in + cs.n_aux);
         }
+        // write_cached_params (parameter_cache.hpp:147-153): the resident key + vk as a bellperson-layout
+        // `.params` file; `filtered` drops the points at infinity from a / b_g1 / b_g2 the way bellman's
+        // generator does, so the file is what Filecoin's parameter files look like.
+        void write_cached(const std::string& path, const verification_key_type& vk, bool filtered = true) const {
+            b2g16::context& c = b2g16::context::instance();
+            std::uint64_t shp[5];                                         // log_m, n_cons, n_in, n_aux, n_vars
+            c.check(b2g16_pk_shape(h_, shp));
+            const std::uint64_t nv = shp[4], counts[5] = {nv, nv, nv, shp[3], (std::uint64_t(1) << shp[0]) - 1};
+            const std::size_t width[5] = {96, 96, 192, 96, 96};           // which = 0 a, 1 b_g1, 2 b_g2, 3 l, 4 h
+            std::vector<std::uint8_t> q[5];
+            b2g16_params p;
+            std::memset(&p, 0, sizeof p);
+            std::uint64_t kept[3] = {nv, nv, nv};
+            for (int w = 0; w < 5; ++w) {
+                q[w].resize(counts[w] * width[w]);
+                c.check(b2g16_pk_export(c.get(), h_, w, q[w].data(), q[w].size()));
+                if (filtered && w < 3) {
+                    std::vector<std::uint8_t> f(q[w].size());
+                    c.check(b2g16_query_filter(q[w].data(), nv, width[w], f.data(), nullptr, &kept[w]));
+                    f.resize(kept[w] * width[w]);
+                    q[w].swap(f);
+                }
+            }
+            std::uint8_t* single[5] = {p.alpha_g1, p.beta_g1, p.delta_g1, p.beta_g2, p.delta_g2};   // which = 5..9
+            const std::size_t sw[5] = {96, 96, 96, 192, 192};
+            for (int w = 0; w < 5; ++w) c.check(b2g16_pk_export(c.get(), h_, 5 + w, single[w], sw[w]));
+            std::memcpy(p.gamma_g2, vk.gamma_g2.data.data(), 192);
+            p.n_ic = vk.gamma_ABC_g1.size(); p.ic = const_cast<std::uint8_t*>(reinterpret_cast<const std::uint8_t*>(vk.gamma_ABC_g1.data()));
+            p.n_a = kept[0]; p.a = q[0].data(); p.n_b_g1 = kept[1]; p.b_g1 = q[1].data(); p.n_b_g2 = kept[2]; p.b_g2 = q[2].data();
+            p.n_l = counts[3]; p.l = q[3].data(); p.n_h = counts[4]; p.h = q[4].data();
+            int rc = b2g16_params_write(path.c_str(), &p);
+            if (rc != B2G16_OK) throw b2g16::error(rc, "cannot write " + path);
+        }
+        // read_cached_params (parameter_cache.hpp:125-129): `.params` file -> resident key (+ the vk it
+        // carries).  Dense files load as they are; density-filtered a / b queries are expanded with the
+        // column occupancy of the constraint system's A / B (a file that does not fit it is refused).
+        static proving_key_type read_cached(const constraint_system_type& cs, const std::string& path, verification_key_type* vk_out = nullptr) {
+            b2g16::context& c = b2g16::context::instance();
+            b2g16_params* p = nullptr;
+            int rc = b2g16_params_read(path.c_str(), &p);
+            if (rc != B2G16_OK) throw b2g16::error(rc, "cannot read " + path);
+            struct guard { b2g16_params* p; ~guard() { b2g16_params_free(p); } } g{p};
+            const std::uint64_t nv = 1 + cs.n_in + cs.n_aux;
+            if (p->n_l != cs.n_aux || p->n_h + 1 != (std::uint64_t(1) << cs.log_m) || p->n_ic != cs.n_in + 1)
+                throw b2g16::error(B2G16_E_INVALID_ARG, path + ": parameters of another circuit (l / h / ic lengths)");
+            b2g16_r1cs_view rv = cs.view();
+            std::vector<std::uint8_t> store[3], dens(nv);
+            auto dense = [&](const std::uint8_t* q, std::uint64_t n, const b2g16_csr& m, std::size_t w, std::vector<std::uint8_t>& s) {
+                if (n == nv) return q;
+                if (b2g16_csr_density(&m, nv, dens.data(), nullptr) != B2G16_OK) throw b2g16::error(B2G16_E_INVALID_ARG, "constraint system: column out of range");
+                s.resize(nv * w);
+                if (b2g16_query_expand(q, n, dens.data(), nv, w, s.data()) != B2G16_OK)
+                    throw b2g16::error(B2G16_E_INVALID_ARG, path + ": filtered query does not match the constraint system's density");
+                return static_cast<const std::uint8_t*>(s.data());
+            };
+            b2g16_pk_view v;
+            v.alpha_g1 = p->alpha_g1; v.beta_g1 = p->beta_g1; v.delta_g1 = p->delta_g1; v.beta_g2 = p->beta_g2; v.delta_g2 = p->delta_g2;
+            v.a = dense(p->a, p->n_a, rv.A, 96, store[0]);
+            v.b_g1 = dense(p->b_g1, p->n_b_g1, rv.B, 96, store[1]);
+            v.b_g2 = dense(p->b_g2, p->n_b_g2, rv.B, 192, store[2]);
+            v.l = p->l; v.h = p->h; v.cs = &rv;
+            b2g16_pk* pk = nullptr;
+            c.check(b2g16_pk_load(c.get(), &v, &pk));
+            if (vk_out) {
+                std::memcpy(vk_out->alpha_g1.data.data(), p->alpha_g1, 96); std::memcpy(vk_out->beta_g2.data.data(), p->beta_g2, 192);
+                std::memcpy(vk_out->gamma_g2.data.data(), p->gamma_g2, 192); std::memcpy(vk_out->delta_g2.data.data(), p->delta_g2, 192);
+                vk_out->gamma_ABC_g1.resize(p->n_ic);
+                std::memcpy(vk_out->gamma_ABC_g1.data(), p->ic, 96 * p->n_ic);
+            }
+            return proving_key_type(pk, nv);
+        }
     };
     struct keypair_type { proving_key_type first; verification_key_type second; };
 };

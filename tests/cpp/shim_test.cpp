@@ -97,6 +97,26 @@ int main(int argc, char** argv) {
         bool threw = false;
         try { scheme::proof_type::read(buf); } catch (const b2g16::error&) { threw = true; }
         expect(threw, "proof read: malformed encoding throws");
+        // the parameter cache (parameter_cache.hpp:125-153): key -> .params file (bellman-style filtered, and dense) -> key
+        for (int filtered = 1; filtered >= 0; --filtered) {
+            std::string path = dir + (filtered ? "/v28-shim-filtered.params" : "/v28-shim-dense.params");
+            kp.first.write_cached(path, kp.second, filtered != 0);
+            scheme::verification_key_type vk2;
+            auto pk2 = scheme::proving_key_type::read_cached(cs, path, &vk2);
+            auto p3 = zk::snark::prove<scheme>(pk2, primary, aux, rs[0], rs[1]);
+            expect(memcmp(p3.bytes().data(), want.data(), 192) == 0, filtered ? "key from a density-filtered .params file: same proof" : "key from a dense .params file: same proof");
+            expect(vk2.gamma_ABC_g1 == kp.second.gamma_ABC_g1 && vk2.gamma_g2 == kp.second.gamma_g2 && vk2.alpha_g1 == kp.second.alpha_g1, "vk carried by the .params file");
+        }
+        {
+            auto other = cs; other.n_aux -= 1;
+            threw = false;
+            try { scheme::proving_key_type::read_cached(other, dir + "/v28-shim-filtered.params"); } catch (const b2g16::error&) { threw = true; }
+            expect(threw, "parameters of another circuit are refused");
+            FILE* a = fopen((dir + "/v28-shim-filtered.params").c_str(), "rb"); FILE* b = fopen((dir + "/v28-shim-dense.params").c_str(), "rb");
+            fseek(a, 0, SEEK_END); fseek(b, 0, SEEK_END);
+            expect(ftell(a) < ftell(b), "filtered file is smaller than the dense one");
+            fclose(a); fclose(b);
+        }
     }
     printf("%s\n", fails ? "SHIM TEST FAILED" : "shim test passed");
     return fails ? 1 : 0;
