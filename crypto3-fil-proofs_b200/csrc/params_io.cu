@@ -16,35 +16,52 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <atomic>
 #include <new>
+#include <thread>
+#include <vector>
 
 #include "../../include/b2g16.h"
 
 namespace {
 
-void be_to_le48(const uint8_t* be, uint8_t* le) { for (int i = 0; i < 48; ++i) le[i] = be[47 - i]; }
+// reverse 48 bytes (BE <-> LE field element) a word at a time
+inline void rev48(const uint8_t* in, uint8_t* out) {
+    uint64_t w[6];
+    memcpy(w, in, 48);
+    uint64_t r[6];
+    for (int i = 0; i < 6; ++i) r[i] = __builtin_bswap64(w[5 - i]);
+    memcpy(out, r, 48);
+}
+inline bool all_zero(const uint8_t* a, size_t n) {
+    uint64_t acc = 0, w;
+    for (size_t i = 0; i < n; i += 8) { memcpy(&w, a + i, 8); acc |= w; }
+    return acc == 0;
+}
 
-// file G1 (x y, BE) -> ABI (x y, LE); infinity -> all zero.  false on a malformed flag byte.
+// file G1 (x y, BE) -> ABI (x y, LE); infinity -> all zero.  false on a malformed flag byte.  In place is fine (in == out).
 bool g1_file_to_abi(const uint8_t* f, uint8_t* a) {
     if (f[0] & 0x80) return false;
     if (f[0] & 0x40) { memset(a, 0, 96); return true; }
-    be_to_le48(f, a); be_to_le48(f + 48, a + 48); return true;
+    rev48(f, a); rev48(f + 48, a + 48); return true;
 }
 void g1_abi_to_file(const uint8_t* a, uint8_t* f) {
-    bool z = true; for (int i = 0; i < 96; ++i) z = z && a[i] == 0;
-    if (z) { memset(f, 0, 96); f[0] = 0x40; return; }
-    be_to_le48(a, f); be_to_le48(a + 48, f + 48);
+    if (all_zero(a, 96)) { memset(f, 0, 96); f[0] = 0x40; return; }
+    rev48(a, f); rev48(a + 48, f + 48);
 }
 // file G2 (x.c1 x.c0 y.c1 y.c0, BE) -> ABI (x.c0 x.c1 y.c0 y.c1, LE)
 bool g2_file_to_abi(const uint8_t* f, uint8_t* a) {
     if (f[0] & 0x80) return false;
     if (f[0] & 0x40) { memset(a, 0, 192); return true; }
-    be_to_le48(f, a + 48); be_to_le48(f + 48, a); be_to_le48(f + 96, a + 144); be_to_le48(f + 144, a + 96); return true;
+    uint8_t t[192];
+    rev48(f, t + 48); rev48(f + 48, t); rev48(f + 96, t + 144); rev48(f + 144, t + 96);
+    memcpy(a, t, 192); return true;
 }
 void g2_abi_to_file(const uint8_t* a, uint8_t* f) {
-    bool z = true; for (int i = 0; i < 192; ++i) z = z && a[i] == 0;
-    if (z) { memset(f, 0, 192); f[0] = 0x40; return; }
-    be_to_le48(a + 48, f); be_to_le48(a, f + 48); be_to_le48(a + 144, f + 96); be_to_le48(a + 96, f + 144);
+    if (all_zero(a, 192)) { memset(f, 0, 192); f[0] = 0x40; return; }
+    uint8_t t[192];
+    rev48(a + 48, t); rev48(a, t + 48); rev48(a + 144, t + 96); rev48(a + 96, t + 144);
+    memcpy(f, t, 192);
 }
 
 struct File {
@@ -56,33 +73,55 @@ struct File {
 bool read_u32_be(FILE* f, uint64_t* v) { uint8_t b[4]; if (fread(b, 1, 4, f) != 4) return false; *v = ((uint32_t)b[0] << 24) | (b[1] << 16) | (b[2] << 8) | b[3]; return true; }
 bool write_u32_be(FILE* f, uint64_t v) { uint8_t b[4] = {(uint8_t)(v >> 24), (uint8_t)(v >> 16), (uint8_t)(v >> 8), (uint8_t)v}; return fwrite(b, 1, 4, f) == 4; }
 
-// one array: n points of `fb` file bytes each -> freshly malloc'ed ABI buffer
+// A 32 GiB-sector key is ~80 GB of points: split the byte shuffles over the host cores.
+template <class Fn> void parallel_ranges(uint64_t n, Fn fn) {
+    unsigned t = std::thread::hardware_concurrency();
+    t = t ? (t > 32 ? 32 : t) : 1;
+    if (n < (1u << 16) || t == 1) { fn(0, n); return; }
+    std::vector<std::thread> th;
+    const uint64_t per = (n + t - 1) / t;
+    for (unsigned k = 0; k < t; ++k) {
+        const uint64_t lo = k * per, hi = lo + per < n ? lo + per : n;
+        if (lo >= hi) break;
+        th.emplace_back([=] { fn(lo, hi); });
+    }
+    for (auto& x : th) x.join();
+}
+
+// one array: n points -> freshly malloc'ed ABI buffer (read whole, converted in place)
 int read_points(FILE* f, uint64_t n, int g2, uint8_t** out) {
-    const size_t sz = g2 ? 192 : 96, CH = 4096;
+    const size_t sz = g2 ? 192 : 96;
+    // the length prefix comes from the file: refuse one the file cannot hold before allocating for it
+    const long at = ftell(f);
+    if (at < 0 || fseek(f, 0, SEEK_END) != 0) return B2G16_E_INVALID_ARG;
+    const long end = ftell(f);
+    if (end < 0 || fseek(f, at, SEEK_SET) != 0 || (uint64_t)(end - at) < n * sz) return B2G16_E_INVALID_ARG;
     uint8_t* buf = (uint8_t*)malloc(n ? n * sz : 1);
     if (!buf) return B2G16_E_OOM;
-    uint8_t* tmp = (uint8_t*)malloc(CH * sz);
-    if (!tmp) { free(buf); return B2G16_E_OOM; }
-    int rc = B2G16_OK;
-    for (uint64_t i = 0; i < n && rc == B2G16_OK; i += CH) {
-        const size_t k = (size_t)((n - i < CH) ? n - i : CH);
-        if (fread(tmp, sz, k, f) != k) { rc = B2G16_E_INVALID_ARG; break; }
-        for (size_t j = 0; j < k; ++j) {
-            const bool ok = g2 ? g2_file_to_abi(tmp + j * sz, buf + (i + j) * sz) : g1_file_to_abi(tmp + j * sz, buf + (i + j) * sz);
-            if (!ok) { rc = B2G16_E_NOT_CANONICAL; break; }
+    if (n && fread(buf, sz, n, f) != n) { free(buf); return B2G16_E_INVALID_ARG; }
+    std::atomic<int> bad(0);
+    parallel_ranges(n, [&](uint64_t lo, uint64_t hi) {
+        for (uint64_t i = lo; i < hi; ++i) {
+            uint8_t* p = buf + i * sz;
+            if (!(g2 ? g2_file_to_abi(p, p) : g1_file_to_abi(p, p))) { bad.store(1); return; }
         }
-    }
-    free(tmp);
-    if (rc != B2G16_OK) { free(buf); return rc; }
+    });
+    if (bad.load()) { free(buf); return B2G16_E_NOT_CANONICAL; }
     *out = buf;
-    return rc;
+    return B2G16_OK;
 }
 bool write_points(FILE* f, const uint8_t* abi, uint64_t n, int g2) {
     const size_t sz = g2 ? 192 : 96;
-    uint8_t rec[192];
-    for (uint64_t i = 0; i < n; ++i) {
-        if (g2) g2_abi_to_file(abi + i * sz, rec); else g1_abi_to_file(abi + i * sz, rec);
-        if (fwrite(rec, 1, sz, f) != sz) return false;
+    const uint64_t CH = 1u << 20;                                  // points per write
+    std::vector<uint8_t> rec((size_t)((n < CH ? n : CH) * sz));
+    for (uint64_t i = 0; i < n; i += CH) {
+        const uint64_t k = n - i < CH ? n - i : CH;
+        parallel_ranges(k, [&](uint64_t lo, uint64_t hi) {
+            for (uint64_t j = lo; j < hi; ++j) {
+                if (g2) g2_abi_to_file(abi + (i + j) * sz, rec.data() + j * sz); else g1_abi_to_file(abi + (i + j) * sz, rec.data() + j * sz);
+            }
+        });
+        if (fwrite(rec.data(), sz, k, f) != k) return false;
     }
     return true;
 }
