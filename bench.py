@@ -318,7 +318,9 @@ def run_b200(args):
         "ms_per_step": ms / args.steps, "higher_is_better": False, "scaling": "weak", "vs_baseline": None,
         "dtype": "u32-limb Montgomery (integer; Fr 8 limbs, Fq 12 limbs)", "data": "synthetic",
         "config": {"workload": args.workload, "describe": WORKLOADS[args.workload][2], "log_m": log_m, "n_in": n_in, "n_cons": shape["n_cons"], "n_vars": nv,
-                   "partitions_per_step_per_gpu": 1, "l2": "inputs larger than L2 (key queries %.0f MB, witness %.0f MB per proof)" % (5 * nv * 96 / 1e6, nv * 32 / 1e6),
+                   "partitions_per_step_per_gpu": 1,
+                   "query_density": "about 0.64 of the a / b_g1 / b_g2 bases are non-identity in this synthetic instance (profiles/r01_key_cache_time_2p22.json); identity bases take no multiexp slot, as with bellman's density-filtered keys; l and h are dense",
+                   "l2": "inputs larger than L2 (key queries %.0f MB, witness %.0f MB per proof)" % (5 * nv * 96 / 1e6, nv * 32 / 1e6),
                    "parallelism": "one partition per GPU, key replicated, no data-path collective"},
         "e2e": {"value": ms_e2e / 1e3 / (args.steps * world), "unit": "s", "h2d_bytes_per_step": nv * 32 + 64, "d2h_bytes_per_step": 192 + 672,
                 "ms_per_step": ms_e2e / args.steps, "api": "b2g16_prove (host witness buffer, pinned)"},

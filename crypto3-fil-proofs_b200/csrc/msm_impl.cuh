@@ -32,9 +32,21 @@ B2_D void load_scalar(const uint32_t* scalars, size_t i, uint32_t* s) {
 }
 
 // ---- 1. histogram ------------------------------------------------------------------
-static __global__ void msm_hist_kernel(const uint32_t* __restrict__ scalars, size_t n, int c, int W, uint32_t* __restrict__ hist) {
+// The dense key layout (scheme_params.hpp:46-66) holds the identity for every variable whose A / B
+// polynomial is zero -- a third or more of the a / b_g1 / b_g2 queries.  bellman filters those points out
+// of its keys; here they are dropped with the zero digits, so they take no slot in the sorted lists and
+// no lane in the accumulate kernel.  q = sizeof(Affine<F>) / 16.
+B2_D bool base_is_identity(const uint4* __restrict__ bases_raw, size_t i, int q) {
+    const uint4* p = bases_raw + i * (size_t)q;
+    uint32_t acc = 0;
+    for (int k = 0; k < q; ++k) { const uint4 v = __ldg(p + k); acc |= v.x | v.y | v.z | v.w; }
+    return acc == 0;
+}
+static __global__ void msm_hist_kernel(const uint32_t* __restrict__ scalars, const uint4* __restrict__ bases_raw, int q, size_t n, int c, int W,
+                                       uint32_t* __restrict__ hist) {
     const uint32_t B = 1u << (c - 1);
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        if (base_is_identity(bases_raw, i, q)) continue;
         uint32_t s[8]; load_scalar(scalars, i, s);
         for (int w = 0; w < W; ++w) {
             int d = msm_signed_digit(s, w, c);
@@ -43,9 +55,11 @@ static __global__ void msm_hist_kernel(const uint32_t* __restrict__ scalars, siz
     }
 }
 // ---- 3. scatter --------------------------------------------------------------------
-static __global__ void msm_scatter_kernel(const uint32_t* __restrict__ scalars, size_t n, int c, int W, uint32_t* __restrict__ cursor, uint32_t* __restrict__ sorted) {
+static __global__ void msm_scatter_kernel(const uint32_t* __restrict__ scalars, const uint4* __restrict__ bases_raw, int q, size_t n, int c, int W,
+                                          uint32_t* __restrict__ cursor, uint32_t* __restrict__ sorted) {
     const uint32_t B = 1u << (c - 1);
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        if (base_is_identity(bases_raw, i, q)) continue;
         uint32_t s[8]; load_scalar(scalars, i, s);
         for (int w = 0; w < W; ++w) {
             int d = msm_signed_digit(s, w, c);
@@ -540,13 +554,16 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
 
     mark(0);
     B2_CUDA(cudaMemsetAsync(hist.get(), 0, (nb + 1) * sizeof(uint32_t), st));
-    msm_hist_kernel<<<grid_for(n, 256, 148 * 8), 256, 0, st>>>(d_scalars, n, c, W, hist.get()); ctx->launches++;
+    static_assert(sizeof(Affine<F>) % 16 == 0, "bases are read as uint4");
+    const uint4* bases_raw = reinterpret_cast<const uint4*>(d_bases);
+    const int base_q = (int)(sizeof(Affine<F>) / 16);
+    msm_hist_kernel<<<grid_for(n, 256, 148 * 8), 256, 0, st>>>(d_scalars, bases_raw, base_q, n, c, W, hist.get()); ctx->launches++;
     mark(1);
     scan_u32(ctx, st, hist.get(), off.get(), nb, 0, 1, tile_sums.get());
     if (!chunked) scan_u32(ctx, st, hist.get(), seg_off.get(), nb, 1, S, tile_sums.get());
     B2_CUDA(cudaMemcpyAsync(cursor.get(), off.get(), (nb + 1) * sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
     mark(2);
-    msm_scatter_kernel<<<grid_for(n, 256, 148 * 8), 256, 0, st>>>(d_scalars, n, c, W, cursor.get(), sorted.get()); ctx->launches++;
+    msm_scatter_kernel<<<grid_for(n, 256, 148 * 8), 256, 0, st>>>(d_scalars, bases_raw, base_q, n, c, W, cursor.get(), sorted.get()); ctx->launches++;
     mark(3);
     if (chunked) {
         B2_CUDA(cudaMemsetAsync(seg_acc.get(), 0, nb * sizeof(Xyzz<F>), st));            // empty bucket = identity (ZZ = 0)
