@@ -46,8 +46,8 @@ static __global__ void msm_hist_kernel(const uint32_t* __restrict__ scalars, con
                                        uint32_t* __restrict__ hist) {
     const uint32_t B = 1u << (c - 1);
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
-        if (base_is_identity(bases_raw, i, q)) continue;
         uint32_t s[8]; load_scalar(scalars, i, s);
+        if ((s[0] | s[1] | s[2] | s[3] | s[4] | s[5] | s[6] | s[7]) == 0 || base_is_identity(bases_raw, i, q)) continue;   // zero scalar: base not read
         for (int w = 0; w < W; ++w) {
             int d = msm_signed_digit(s, w, c);
             if (d) atomicAdd(hist + (size_t)w * B + (uint32_t)((d < 0 ? -d : d) - 1), 1u);
@@ -59,8 +59,8 @@ static __global__ void msm_scatter_kernel(const uint32_t* __restrict__ scalars, 
                                           uint32_t* __restrict__ cursor, uint32_t* __restrict__ sorted) {
     const uint32_t B = 1u << (c - 1);
     for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
-        if (base_is_identity(bases_raw, i, q)) continue;
         uint32_t s[8]; load_scalar(scalars, i, s);
+        if ((s[0] | s[1] | s[2] | s[3] | s[4] | s[5] | s[6] | s[7]) == 0 || base_is_identity(bases_raw, i, q)) continue;   // zero scalar: base not read
         for (int w = 0; w < W; ++w) {
             int d = msm_signed_digit(s, w, c);
             if (d) {
