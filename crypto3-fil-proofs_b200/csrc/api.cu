@@ -4,6 +4,7 @@
 #include <new>
 #include <cstdlib>
 #include <cstring>
+#include <string>
 #include "common.cuh"
 #include "api_util.cuh"
 
@@ -28,6 +29,7 @@ int b2g16_init(int device, void* stream, b2g16_ctx** out) {
             B2_CUDA(cudaEventCreateWithFlags(&c->ev_join[i], cudaEventDisableTiming));
         }
         B2_CUDA(cudaEventCreateWithFlags(&c->ev_fork, cudaEventDisableTiming));
+        for (auto& e : c->ev_stage) B2_CUDA(cudaEventCreate(&e));
         cudaMemPool_t pool;
         B2_CUDA(cudaDeviceGetDefaultMemPool(&pool, device));
         uint64_t keep = ~0ull;                                      // keep freed workspace in the pool
@@ -52,6 +54,9 @@ int b2g16_shutdown(b2g16_ctx* h) {
     for (int i = 0; i < 2; ++i) cudaFree(c->fixed_base[i]);
     for (int i = 0; i < 4; ++i) { cudaStreamDestroy(c->aux[i]); cudaEventDestroy(c->ev_join[i]); }
     cudaEventDestroy(c->ev_fork);
+    for (auto& e : c->ev_stage) cudaEventDestroy(e);
+    for (auto& e : c->klog) { cudaEventDestroy(e.e0); cudaEventDestroy(e.e1); }
+    cudaFree(c->d_klog_entries);
     if (c->own_stream) cudaStreamDestroy(c->stream);
     delete c;
     return B2G16_OK;
@@ -83,12 +88,13 @@ static int bases_upload(b2g16_ctx* h, int group, const uint8_t* bytes, size_t n,
         void* d_pts = nullptr;
         if (n) B2_CUDA(cudaMalloc(&d_pts, n * enc));
         try {
-            DevBuf<uint8_t> raw(n * enc, c->stream);
             DevFlag bad(c);
             if (n) {
-                B2_CUDA(cudaMemcpyAsync(raw.get(), bytes, n * enc, cudaMemcpyHostToDevice, c->stream));
-                if (group == 1) g1_from_bytes_dev(c, raw.get(), (G1Affine*)d_pts, n, bad.ptr(), true);
-                else g2_from_bytes_dev(c, raw.get(), (G2Affine*)d_pts, n, bad.ptr(), true);
+                // ABI bytes and Montgomery limbs have the same size: upload into place, convert in place (one thread
+                // reads its whole point before it writes it) -- no second n * enc staging buffer for 72 GiB-class keys
+                B2_CUDA(cudaMemcpyAsync(d_pts, bytes, n * enc, cudaMemcpyHostToDevice, c->stream));
+                if (group == 1) g1_from_bytes_dev(c, (const uint8_t*)d_pts, (G1Affine*)d_pts, n, bad.ptr(), true);
+                else g2_from_bytes_dev(c, (const uint8_t*)d_pts, (G2Affine*)d_pts, n, bad.ptr(), true);
             }
             bad.check("bases");
         } catch (...) { cudaFree(d_pts); throw; }
@@ -118,7 +124,7 @@ int b2g16_bases_generate(b2g16_ctx* h, int group, const uint8_t* d_scalars32, si
 
 int b2g16_bases_download(b2g16_ctx* h, const b2g16_bases* b, size_t first, size_t count, uint8_t* out) {
     Ctx* c = reinterpret_cast<Ctx*>(h);
-    if (!c || !b || (count && !out) || first + count > b->n) return B2G16_E_INVALID_ARG;
+    if (!c || !b || (count && !out) || first > b->n || count > b->n - first) return B2G16_E_INVALID_ARG;
     return guard(c, [&] {
         if (!count) return;
         const size_t enc = b->group == 1 ? 96 : 192;
@@ -148,13 +154,13 @@ static void msm_any(Ctx* c, const b2g16_bases* b, size_t first, const uint8_t* d
 
 int b2g16_msm_resident_async(b2g16_ctx* h, const b2g16_bases* b, size_t first, const uint8_t* d_scalars32, size_t n, uint8_t* d_out_affine) {
     Ctx* c = reinterpret_cast<Ctx*>(h);
-    if (!c || !b || !d_out_affine || (n && !d_scalars32) || first + n > b->n) return B2G16_E_INVALID_ARG;
+    if (!c || !b || !d_out_affine || (n && !d_scalars32) || first > b->n || n > b->n - first) return B2G16_E_INVALID_ARG;
     return guard(c, [&] { msm_any(c, b, first, d_scalars32, n, d_out_affine, c->stream); });
 }
 
 int b2g16_msm_resident(b2g16_ctx* h, const b2g16_bases* b, size_t first, const uint8_t* d_scalars32, size_t n, uint8_t* out_affine) {
     Ctx* c = reinterpret_cast<Ctx*>(h);
-    if (!c || !b || !out_affine || (n && !d_scalars32) || first + n > b->n) return B2G16_E_INVALID_ARG;
+    if (!c || !b || !out_affine || (n && !d_scalars32) || first > b->n || n > b->n - first) return B2G16_E_INVALID_ARG;
     return guard(c, [&] {
         const size_t enc = b->group == 1 ? 96 : 192;
         DevBuf<uint8_t> d_out(enc, c->stream);
@@ -347,6 +353,18 @@ int b2g16_field_op(b2g16_ctx* h, int field, int op, const uint8_t* a, const uint
     });
 }
 
+int b2g16_fr_dot_device(b2g16_ctx* h, const uint8_t* d_a32, const uint8_t* d_b32, size_t n, uint8_t out32[32]) {
+    Ctx* c = reinterpret_cast<Ctx*>(h);
+    if (!c || !out32 || (n && (!d_a32 || !d_b32))) return B2G16_E_INVALID_ARG;
+    return guard(c, [&] {
+        DevBuf<uint8_t> d_out(32, c->stream);
+        DevFlag bad(c);
+        fr_dot_dev(c, d_a32, d_b32, n, d_out.get(), bad.ptr());
+        B2_CUDA(cudaMemcpyAsync(out32, d_out.get(), 32, cudaMemcpyDeviceToHost, c->stream));
+        bad.check("scalars");
+    });
+}
+
 int b2g16_measure_mad32_peak(b2g16_ctx* h, double* mad32_per_s, double* elapsed_ms) {
     Ctx* c = reinterpret_cast<Ctx*>(h);
     if (!c || !mad32_per_s) return B2G16_E_INVALID_ARG;
@@ -363,6 +381,48 @@ int b2g16_set_msm_timing(b2g16_ctx* h, int enabled) {
     if (!c) return B2G16_E_INVALID_ARG;
     c->time_msm = enabled != 0;
     return B2G16_OK;
+}
+// Tuning / measurement knobs by name (the same ones b2g16_init reads from B2G16_* environment variables).
+int b2g16_set_tuning(b2g16_ctx* h, const char* key, int value) {
+    Ctx* c = reinterpret_cast<Ctx*>(h);
+    if (!c || !key) return B2G16_E_INVALID_ARG;
+    std::lock_guard<std::mutex> lock(c->mu);
+    const std::string k(key);
+    if (k == "serial_above_log") c->serial_above_log = value;
+    else if (k == "red_log" && value >= 1 && value <= 6) c->red_log = value;
+    else if (k == "acc_variant") c->acc_variant = value;
+    else if (k == "kernel_log") {
+        c->klog_on = value != 0;
+        cudaSetDevice(c->device);
+        if (c->klog_on && !c->d_klog_entries && cudaMalloc((void**)&c->d_klog_entries, 64 * sizeof(uint32_t)) != cudaSuccess) return B2G16_E_OOM;
+        for (auto& e : c->klog) { cudaEventDestroy(e.e0); cudaEventDestroy(e.e1); }
+        c->klog.clear();
+    } else return B2G16_E_INVALID_ARG;
+    return B2G16_OK;
+}
+// Drains the accumulate-kernel launch log: out[5 * i ..] = { group (1|2), window bits, points, kernel milliseconds,
+// sorted (point, window) entries = additions the launch performed };
+// returns the number of entries written (at most max_entries) or a negative error.  Synchronises the device.
+int b2g16_kernel_log(b2g16_ctx* h, double* out, int max_entries) {
+    Ctx* c = reinterpret_cast<Ctx*>(h);
+    if (!c || (max_entries > 0 && !out)) return B2G16_E_INVALID_ARG;
+    int n = 0;
+    int rc = guard(c, [&] {
+        B2_CUDA(cudaDeviceSynchronize());
+        uint32_t entries[64] = {};
+        if (c->d_klog_entries) B2_CUDA(cudaMemcpy(entries, c->d_klog_entries, sizeof entries, cudaMemcpyDeviceToHost));
+        for (auto& e : c->klog) {
+            float ms = 0.f;
+            if (n < max_entries) {
+                B2_CUDA(cudaEventElapsedTime(&ms, e.e0, e.e1));
+                out[5 * n] = e.group; out[5 * n + 1] = e.c; out[5 * n + 2] = (double)e.n; out[5 * n + 3] = ms; out[5 * n + 4] = n < 64 ? entries[n] : 0;
+                ++n;
+            }
+            cudaEventDestroy(e.e0); cudaEventDestroy(e.e1);
+        }
+        c->klog.clear();
+    });
+    return rc == B2G16_OK ? n : rc;
 }
 int b2g16_set_msm_window(b2g16_ctx* h, int window_bits) {
     Ctx* c = reinterpret_cast<Ctx*>(h);

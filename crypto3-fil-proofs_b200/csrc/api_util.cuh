@@ -40,6 +40,7 @@ struct DevFlag {
         B2_CUDA(cudaStreamSynchronize(c->stream));
         if (v & 1) throw ArgError{B2G16_E_NOT_CANONICAL, std::string(what) + ": value not canonical (>= modulus)"};
         if (v & 2) throw ArgError{B2G16_E_NOT_ON_CURVE, std::string(what) + ": point not on curve"};
+        if (v & 4) throw ArgError{B2G16_E_NOT_ON_CURVE, std::string(what) + ": point not in the prime-order subgroup"};
     }
 };
 

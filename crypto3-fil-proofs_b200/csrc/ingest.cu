@@ -98,6 +98,34 @@ template <class F> __global__ void __launch_bounds__(128) field_op_kernel(int op
     if (bad && d_bad) atomicOr(d_bad, bad);
 }
 
+// out = sum_i a_i b_i mod r over canonical scalars (measurement aid: the scalar side of the multiexp linearity identity
+// sum_i s_i (k_i G) = (sum_i s_i k_i) G that bench.py checks at 2^26 points).  A Montgomery product of two canonical
+// operands is a b / R; the partial sums stay in that form and one product with R^2 at the end restores the plain residue.
+__global__ void __launch_bounds__(256) fr_dot_partial_kernel(const uint8_t* a, const uint8_t* b, size_t n, Fr* partial, int* d_bad) {
+    __shared__ Fr sh[256];
+    Fr acc = Fr::zero();
+    int bad = 0;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        Fr x = load_limbs<Fr>(a + 32 * i), y = load_limbs<Fr>(b + 32 * i);
+        if (Fr::geq_p(x.v) || Fr::geq_p(y.v)) bad = 1;
+        acc = acc + x * y;
+    }
+    if (bad && d_bad) atomicOr(d_bad, 1);
+    sh[threadIdx.x] = acc;
+    __syncthreads();
+    for (int d = 128; d >= 1; d >>= 1) {
+        if ((int)threadIdx.x < d) sh[threadIdx.x] = sh[threadIdx.x] + sh[threadIdx.x + d];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) fr_store(partial + blockIdx.x, sh[0]);
+}
+__global__ void __launch_bounds__(32) fr_dot_final_kernel(const Fr* partial, int count, uint8_t* out32) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    Fr acc = Fr::zero();
+    for (int i = 0; i < count; ++i) acc = acc + fr_load(partial + i);
+    store_limbs<Fr>(out32, acc * Fr::r2());
+}
+
 // Sustained 32x32 -> 64 multiply rate of the integer pipe: 8 chains of IMAD.WIDE per thread whose
 // multiplicands are live accumulator halves, so ptxas cannot hoist the product out of the loop
 // (a loop-invariant a*b is folded into IADD3 pairs and would time the ALU pipe instead).
@@ -157,6 +185,13 @@ void field_op_dev(Ctx* c, int field, int op, const uint8_t* d_a, const uint8_t* 
     if (field == 0) field_op_kernel<Fr><<<grid_for(n, 128), 128, 0, c->stream>>>(op, d_a, d_b, n, d_out, d_bad);
     else field_op_kernel<Fq><<<grid_for(n, 128), 128, 0, c->stream>>>(op, d_a, d_b, n, d_out, d_bad);
     check_launch(c);
+}
+
+void fr_dot_dev(Ctx* c, const uint8_t* d_a, const uint8_t* d_b, size_t n, uint8_t* d_out32, int* d_bad) {
+    const int blocks = grid_for(n, 256, 148 * 8);
+    DevBuf<Fr> partial(blocks, c->stream);
+    fr_dot_partial_kernel<<<blocks, 256, 0, c->stream>>>(d_a, d_b, n, partial.get(), d_bad); check_launch(c);
+    fr_dot_final_kernel<<<1, 32, 0, c->stream>>>(partial.get(), blocks, d_out32); check_launch(c);
 }
 
 double mad32_peak_dev(Ctx* c, double* elapsed_ms) {

@@ -23,6 +23,12 @@ void gen_mul_g1_dev(Ctx* c, const uint32_t* d_scalars, size_t n, G1Affine* d_out
     c->launches++;
     B2_CUDA(cudaGetLastError());
 }
+void g1_subgroup_check_dev(Ctx* c, const G1Affine* d_pts, size_t n, int* d_bad) {
+    if (!n) return;
+    subgroup_check_kernel<Fq><<<grid_for(n, 64), 64, 0, c->stream>>>(d_pts, n, d_bad);
+    c->launches++;
+    B2_CUDA(cudaGetLastError());
+}
 void sum_g1_dev(Ctx* c, const G1Affine* d_pts, size_t n, uint8_t* d_out_bytes) {
     sum_points_kernel<Fq><<<1, 32, 0, c->stream>>>(d_pts, n, d_out_bytes);
     c->launches++;

@@ -404,6 +404,20 @@ sum_points_kernel(const Affine<F>* __restrict__ pts, size_t n, uint8_t* __restri
     egress_affine(out_bytes, aff);
 }
 
+// prime-order subgroup membership r * P == O for each point (verifying-key IC points, as bellman's VerifyingKey::read
+// checks them); sets bit 2 of *bad.  Double-and-add over the 255 bits of r, one thread per point.
+template <class F> __global__ void __launch_bounds__(64) subgroup_check_kernel(const Affine<F>* __restrict__ pts, size_t n, int* bad) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) {
+        const Affine<F> p = pts[i];
+        Xyzz<F> acc = Xyzz<F>::identity();
+        for (int bit = 254; bit >= 0; --bit) {
+            xyzz_dbl_call(&acc);
+            if ((FrParams::P(bit >> 5) >> (bit & 31)) & 1u) xyzz_add_mixed_call(&acc, &p);
+        }
+        if (!acc.is_identity()) atomicOr(bad, 4);
+    }
+}
+
 // ---- fixed-base multiples of the group generator (synthetic bases, Groth16 setup) -------
 // table[w * 255 + (d-1)] = d * 2^(8w) * G, affine, w < 32
 template <class F> __global__ void __launch_bounds__(32) fixed_base_roots_kernel(Affine<F> gen, Affine<F>* roots /*32*/) {
@@ -565,11 +579,14 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
     mark(2);
     msm_scatter_kernel<<<grid_for(n, 256, 148 * 8), 256, 0, st>>>(d_scalars, bases_raw, base_q, n, c, W, cursor.get(), sorted.get()); ctx->launches++;
     mark(3);
+    Ctx::KernelLogEntry kl{sizeof(F) > 48 ? 2 : 1, c, (uint64_t)n, nullptr, nullptr};
+    if (ctx->klog_on) { B2_CUDA(cudaEventCreate(&kl.e0)); B2_CUDA(cudaEventCreate(&kl.e1)); }
     if (chunked) {
         B2_CUDA(cudaMemsetAsync(seg_acc.get(), 0, nb * sizeof(Xyzz<F>), st));            // empty bucket = identity (ZZ = 0)
         Xyzz<F>* head = pieces.get(); Xyzz<F>* tail = pieces.get() + n_chunks;
         uint32_t* hb = piece_bucket.get(); uint32_t* tb = piece_bucket.get() + n_chunks;
 #define B2_CH(THREADS, MINB) msm_accumulate_chunked_kernel<F, THREADS, MINB><<<148 * MINB, THREADS, 0, st>>>(d_bases, sorted.get(), off.get(), (uint32_t)nb, seg_acc.get(), head, tail, hb, tb)
+        if (kl.e0) B2_CUDA(cudaEventRecord(kl.e0, st));
         if (sizeof(F) > 48) B2_CH(64, 4);
         else switch (ctx->acc_variant) {
             case 101: B2_CH(128, 1); break;
@@ -581,11 +598,19 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
             default: B2_REQUIRE(false, B2G16_E_INVALID_ARG, "msm: chunked accumulate variant must be 101..106");
         }
 #undef B2_CH
+        if (kl.e1) B2_CUDA(cudaEventRecord(kl.e1, st));
         msm_fix_pieces_kernel<F><<<grid_for((size_t)n_chunks * 32, 128, 148 * 16), 128, 0, st>>>(seg_acc.get(), head, tail, hb, tb, n_chunks);
         ctx->launches += 2;
     } else {
+        if (kl.e0) B2_CUDA(cudaEventRecord(kl.e0, st));
         launch_accumulate<F>(ctx, st, max_segs, d_bases, sorted.get(), hist.get(), off.get(), seg_off.get(), (uint32_t)nb, S, seg_acc.get());
+        if (kl.e1) B2_CUDA(cudaEventRecord(kl.e1, st));
         msm_fold_segments_kernel<F><<<grid_for(nb * 32, 128, 148 * 16), 128, 0, st>>>(seg_acc.get(), seg_off.get(), (uint32_t)nb); ctx->launches++;
+    }
+    if (kl.e0) {
+        if (ctx->d_klog_entries && ctx->klog.size() < 64)
+            B2_CUDA(cudaMemcpyAsync(ctx->d_klog_entries + ctx->klog.size(), off.get() + nb, sizeof(uint32_t), cudaMemcpyDeviceToDevice, st));
+        ctx->klog.push_back(kl);
     }
     mark(4);
     const Xyzz<F>* win = nullptr;
@@ -605,7 +630,6 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
         win = a_in;
     } else {
         const uint32_t T = msm_reduce_chunks(c);
-        B2_REQUIRE((size_t)W * T <= (size_t)W * T1 || true, B2G16_E_INTERNAL, "reduce scratch");
         DevBuf<Xyzz<F>> partial((size_t)W * T, st);
         msm_reduce_kernel<F><<<(W * T + 127) / 128, 128, 0, st>>>(seg_acc.get(), seg_off.get(), c, W, T, partial.get()); ctx->launches++;
         msm_window_sum_kernel<F><<<W, 32, 0, st>>>(partial.get(), T, red_a[0].get()); ctx->launches++;

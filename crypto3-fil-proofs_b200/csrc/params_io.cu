@@ -190,9 +190,13 @@ int b2g16_params_vk_bytes(const b2g16_params* p, uint8_t* vk_out, size_t vk_byte
 // its prover skips them through the a_aux / b_input / b_aux density bitmaps) <-> the dense layout of
 // scheme_params.hpp:46-66 that b2g16_pk_view takes.  A column's polynomial is zero exactly when the
 // variable occurs in no row, so the bitmap is the column occupancy of the matrix.
-int b2g16_csr_density(const b2g16_csr* m, uint64_t n_vars, uint8_t* density_out, uint64_t* count_out) {
-    if (!m || !density_out || (m->nnz && !m->col)) return B2G16_E_INVALID_ARG;
+int b2g16_query_density(const b2g16_csr* m, uint64_t n_vars, uint64_t n_always, uint8_t* density_out, uint64_t* count_out) {
+    if (!m || !density_out || (m->nnz && !m->col) || n_always > n_vars) return B2G16_E_INVALID_ARG;
     memset(density_out, 0, n_vars);
+    // The a query carries the input-consistency rows (u_j += L[n_cons + j] for j <= n_in), so the
+    // polynomial of ONE and of every public input is never zero there, whether or not the variable occurs in a row
+    // of A -- bellman keeps all n_in + 1 of them (its a_inputs density is full).  n_always = n_in + 1 for a, 0 for b.
+    memset(density_out, 1, n_always);
     for (uint64_t k = 0; k < m->nnz; ++k) {
         if (m->col[k] >= n_vars) return B2G16_E_INVALID_ARG;
         density_out[m->col[k]] = 1;
@@ -203,6 +207,9 @@ int b2g16_csr_density(const b2g16_csr* m, uint64_t n_vars, uint8_t* density_out,
         *count_out = c;
     }
     return B2G16_OK;
+}
+int b2g16_csr_density(const b2g16_csr* m, uint64_t n_vars, uint8_t* density_out, uint64_t* count_out) {
+    return b2g16_query_density(m, n_vars, 0, density_out, count_out);
 }
 
 int b2g16_query_expand(const uint8_t* filtered, uint64_t n_filtered, const uint8_t* density, uint64_t n_vars, size_t point_bytes,

@@ -296,8 +296,7 @@ static void prove_one(Ctx* c, const b2g16_pk* pk, const uint8_t* d_z_canon, cons
     auto cnt_of = [&](uint64_t n) { return (size_t)(n * (part + 1) / parts - n * part / parts); };
     const uint64_t m = pk->m, nv = pk->n_vars;
     cudaStream_t st = c->stream;
-    cudaEvent_t ev[5];
-    for (auto& e : ev) B2_CUDA(cudaEventCreate(&e));
+    cudaEvent_t* ev = c->ev_stage;                       // created once per context
     DevFlag bad(c);
     // d_h_slice: H coefficients [h_first, h_first + h_count) computed elsewhere (the sharded witness map): no
     // constraint evaluation and no transforms here, and this rank's share of the H query is exactly that range
@@ -336,7 +335,15 @@ static void prove_one(Ctx* c, const b2g16_pk* pk, const uint8_t* d_z_canon, cons
         }
     }
     B2_CUDA(cudaEventRecord(ev[2], st));
-    // witness MSMs do not depend on H: fork them onto the aux streams while the NTT chain runs
+    // witness MSMs do not depend on H: fork them onto the aux streams while the NTT chain runs.  From here to the join,
+    // work of this proof may be running on the aux streams against buffers that are freed stream-ordered on `st`
+    // (d_win, z, the MSM scratch): if anything throws in between (e.g. an out-of-memory in a later multiexp's scratch),
+    // wait for every stream before the buffers' destructors run, or a stale kernel could write into memory the pool has
+    // already handed to the next proof.
+    struct JoinOnUnwind {
+        Ctx* c; bool armed = true;
+        ~JoinOnUnwind() { if (armed) { for (auto s : c->aux) cudaStreamSynchronize(s); cudaStreamSynchronize(c->stream); } }
+    } unwind{c};
     B2_CUDA(cudaEventRecord(c->ev_fork, st));
     for (int i = 0; i < 4; ++i) B2_CUDA(cudaStreamWaitEvent(c->aux[i], c->ev_fork, 0));
     const uint32_t* zc = reinterpret_cast<const uint32_t*>(d_z_canon);
@@ -361,12 +368,12 @@ static void prove_one(Ctx* c, const b2g16_pk* pk, const uint8_t* d_z_canon, cons
     B2_CUDA(cudaMemcpyAsync(&win, dw, sizeof(WinBuf), cudaMemcpyDeviceToHost, st));
     if (tr && tr->h && !ext_h) B2_CUDA(cudaMemcpyAsync(tr->h, h.get(), m * 32, cudaMemcpyDeviceToHost, st));
     B2_CUDA(cudaEventRecord(ev[4], st));
-    bad.check("assignment");                              // synchronises the stream
+    bad.check("assignment");                              // synchronises the stream (which has joined the aux streams)
+    unwind.armed = false;
     if (tr) {
         for (int i = 0; i < 8; ++i) tr->stage_ms[i] = 0.f;
         for (int i = 0; i < 4; ++i) cudaEventElapsedTime(&tr->stage_ms[i], ev[i], ev[i + 1]);   // ingest, abc, ntt/h, msm_h + join of the rest
     }
-    for (auto& e : ev) cudaEventDestroy(e);
     // Horner over the windows of each multiexp, on the host (the stream is idle: bad.check synchronised it);
     // the five combinations are independent: one thread each, the G2 one (3x the work) on this thread
     {

@@ -33,9 +33,11 @@ namespace {
 struct DecodedProof { b2h::G1 a, c; b2h::G2 b; };
 
 // decompress + on-curve (by construction) + prime-order subgroup membership, as bellman's
-// Proof::read does for every proof it deserialises
+// Proof::read does for every proof it deserialises; like Proof::read, the point at infinity is refused for A, B
+// and C (miller_loop would silently skip such a term)
 bool decode_proof(const uint8_t* p, DecodedProof* o) {
     if (!b2h::g1_decompress(p, &o->a) || !b2h::g2_decompress(p + 48, &o->b) || !b2h::g1_decompress(p + 144, &o->c)) return false;
+    if (o->a.inf || o->b.inf || o->c.inf) return false;
     return b2h::in_subgroup(o->a) && b2h::in_subgroup(o->b) && b2h::in_subgroup(o->c);
 }
 
@@ -82,6 +84,7 @@ int b2g16_vk_prepare(b2g16_ctx* h, const uint8_t* vk, size_t n_ic, b2g16_pvk** o
         B2_CUDA(cudaMalloc((void**)&p->d_ic, n_ic * sizeof(G1Affine)));
         B2_CUDA(cudaMemcpyAsync(p->d_ic, vk + 672, n_ic * 96, cudaMemcpyHostToDevice, c->stream));
         g1_from_bytes_dev(c, reinterpret_cast<const uint8_t*>(p->d_ic), p->d_ic, n_ic, bad.ptr(), true);
+        g1_subgroup_check_dev(c, p->d_ic, n_ic, bad.ptr());          // bellman's VerifyingKey::read checks the IC points too
         try { bad.check("vk ic"); } catch (...) { cudaFree(p->d_ic); throw; }
         *out = p.release();
     });

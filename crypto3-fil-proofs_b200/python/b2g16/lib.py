@@ -85,14 +85,15 @@ def params_read(path):
     return out
 
 
-def csr_density(col, n_vars):
-    """b2g16_csr_density: bitmap (uint8, n_vars) of the variables that occur in a matrix given its CSR column indices."""
+def csr_density(col, n_vars, n_always=0):
+    """b2g16_query_density: bitmap (uint8, n_vars) of the variables whose query point is present, given the matrix's CSR
+    column indices; n_always = n_in + 1 for the a query (input-consistency rows), 0 for b_g1 / b_g2."""
     col = np.ascontiguousarray(col, dtype=np.uint32)
     m = Csr(0, col.shape[0], None, _p(col), None)
     out, cnt = np.zeros(n_vars, np.uint8), C.c_uint64()
-    rc = load().b2g16_csr_density(C.byref(m), C.c_uint64(n_vars), _p(out), C.byref(cnt))
+    rc = load().b2g16_query_density(C.byref(m), C.c_uint64(n_vars), C.c_uint64(n_always), _p(out), C.byref(cnt))
     if rc != 0:
-        raise B2g16Error(rc, "b2g16_csr_density: column index out of range")
+        raise B2g16Error(rc, "b2g16_query_density: column index out of range")
     return out, int(cnt.value)
 
 
@@ -352,6 +353,11 @@ class Context:
         self._chk(load().b2g16_field_op(self.h, 0 if field == "fr" else 1, code, _p(a), _p(b), C.c_size_t(a.shape[0]), _p(out)))
         return out
 
+    def fr_dot_device(self, d_a_ptr, d_b_ptr, n):
+        out = np.zeros(32, dtype=np.uint8)
+        self._chk(load().b2g16_fr_dot_device(self.h, C.c_void_p(d_a_ptr), C.c_void_p(d_b_ptr), C.c_size_t(n), _p(out)))
+        return out
+
     def mad32_peak(self):
         v, ms = C.c_double(), C.c_double()
         self._chk(load().b2g16_measure_mad32_peak(self.h, C.byref(v), C.byref(ms)))
@@ -362,6 +368,18 @@ class Context:
 
     def set_msm_window(self, c):
         self._chk(load().b2g16_set_msm_window(self.h, int(c)))
+
+    def set_tuning(self, key, value):
+        self._chk(load().b2g16_set_tuning(self.h, key.encode(), int(value)))
+
+    def kernel_log(self, max_entries=64):
+        """[dict(group, c, n, ms, entries)] of the bucket-accumulation launches since set_tuning("kernel_log", 1)"""
+        out = (C.c_double * (5 * max_entries))()
+        n = load().b2g16_kernel_log(self.h, out, int(max_entries))
+        if n < 0:
+            self._chk(n)
+        return [dict(group=int(out[5 * i]), c=int(out[5 * i + 1]), n=int(out[5 * i + 2]), ms=float(out[5 * i + 3]), entries=int(out[5 * i + 4]))
+                for i in range(n)]
 
     def last_msm_timing(self):
         out = (C.c_float * 5)()

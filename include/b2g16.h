@@ -69,7 +69,10 @@ int b2g16_bases_free(b2g16_ctx*, b2g16_bases*);
 /* scalars already in device memory (32-byte canonical each); result to host.
  * Uses points [first, first+n) of the resident set (MSM range-sharding across ranks). */
 int b2g16_msm_resident(b2g16_ctx*, const b2g16_bases*, size_t first, const uint8_t* d_scalars32, size_t n, uint8_t* out_affine);
-/* same, asynchronous: writes the affine result (96/192 B) to device memory d_out */
+/* same, asynchronous: writes the affine result (96/192 B) to device memory d_out.  PRECONDITION: the scalars are
+ * canonical (< r).  Nothing here can wait for a device-side check, so unlike b2g16_msm_resident this entry point
+ * does not validate them: the signed-digit recoding is exact only below 2^255, and a non-canonical scalar yields a
+ * wrong point, not an error.  Validate once where the scalars are produced, or use the synchronous form. */
 int b2g16_msm_resident_async(b2g16_ctx*, const b2g16_bases*, size_t first, const uint8_t* d_scalars32, size_t n, uint8_t* d_out_affine);
 /* out = sum of n affine points (combining per-GPU partial MSM results after all-gather) */
 int b2g16_g1_sum(b2g16_ctx*, const uint8_t* pts96, size_t n, uint8_t out96[96]);
@@ -250,12 +253,16 @@ int b2g16_params_vk_bytes(const b2g16_params*, uint8_t* vk_out, size_t vk_bytes)
  * prover walks them with the density bitmaps it records during synthesis.  b2g16_pk_view wants the
  * dense crypto3 layout, so a caller holding such a file derives the bitmap from the constraint
  * system it loads anyway and expands:
- *   b2g16_csr_density : density[j] = 1 iff column j (variable j of z) occurs in the matrix; *count_out = popcount
+ *   b2g16_query_density: density[j] = 1 iff j < n_always or column j (variable j of z) occurs in the matrix;
+ *                       *count_out = popcount.  The a query carries the input-consistency rows, so ONE and every
+ *                       public input are always present there: pass n_always = n_in + 1 with A, 0 with B.
+ *   b2g16_csr_density : the n_always = 0 form (plain column occupancy; right for b_g1 / b_g2 only)
  *   b2g16_query_expand: dense[j] = next filtered point if density[j] else identity (zero bytes);
  *                       B2G16_E_INVALID_ARG unless n_filtered equals the number of set entries
  *   b2g16_query_filter: the inverse (drops all-zero points), for writing bellman-style files;
  *                       filtered_out may be NULL to count only
  * point_bytes = 96 (G1) or 192 (G2).  Host-only. */
+int b2g16_query_density(const b2g16_csr* m, uint64_t n_vars, uint64_t n_always, uint8_t* density_out, uint64_t* count_out);
 int b2g16_csr_density(const b2g16_csr* m, uint64_t n_vars, uint8_t* density_out, uint64_t* count_out);
 int b2g16_query_expand(const uint8_t* filtered, uint64_t n_filtered, const uint8_t* density, uint64_t n_vars, size_t point_bytes,
                        uint8_t* dense_out);
@@ -271,10 +278,22 @@ int b2g16_synth_witness(b2g16_ctx*, const b2g16_pk*, uint8_t* d_assignment32, ui
 int b2g16_measure_mad32_peak(b2g16_ctx*, double* mad32_per_s, double* elapsed_ms);
 /* last MSM's per-stage device times in ms: digits+histogram, scan, scatter, accumulate, reduce */
 int b2g16_last_msm_timing(b2g16_ctx*, float out_ms[5]);
+int b2g16_set_msm_timing(b2g16_ctx*, int enabled);
+/* force the Pippenger window width (8..23 bits; 0 = choose by size) */
+int b2g16_set_msm_window(b2g16_ctx*, int window_bits);
+/* knobs by name: "serial_above_log" (proofs with a larger domain run their multiexps one after the other),
+ * "red_log", "acc_variant", "kernel_log" (1 = record CUDA events around every bucket-accumulation launch) */
+int b2g16_set_tuning(b2g16_ctx*, const char* key, int value);
+/* drains the launch log: out[5 i ..] = { group 1|2, window bits, points, kernel ms, (point, window) entries added };
+ * returns the entry count */
+int b2g16_kernel_log(b2g16_ctx*, double* out, int max_entries);
 
 /* ---- elementwise field kernels exposed for parity tests (device does the arithmetic).
  *      field: 0 = Fr (32 B), 1 = Fq (48 B); op: 0 add 1 sub 2 mul 3 inv 4 sqr 5 neg */
 int b2g16_field_op(b2g16_ctx*, int field, int op, const uint8_t* a, const uint8_t* b, size_t n, uint8_t* out);
+/* out = sum_i a_i b_i mod r over device-resident canonical scalars: the scalar side of the multiexp linearity
+ * identity sum_i s_i (k_i G) = (sum_i s_i k_i) G, a size-independent parity property checked at full size */
+int b2g16_fr_dot_device(b2g16_ctx*, const uint8_t* d_a32, const uint8_t* d_b32, size_t n, uint8_t out32[32]);
 
 #ifdef __cplusplus
 }

@@ -303,7 +303,8 @@ template <class CurveType> struct r1cs_gg_ppzksnark {
         }
         // read_cached_params (parameter_cache.hpp:125-129): `.params` file -> resident key (+ the vk it
         // carries).  Dense files load as they are; density-filtered a / b queries are expanded with the
-        // column occupancy of the constraint system's A / B (a file that does not fit it is refused).
+        // column occupancy of the constraint system's A / B -- plus ONE and every public input for a, whose
+        // input-consistency rows make those polynomials non-zero (a file that does not fit is refused).
         static proving_key_type read_cached(const constraint_system_type& cs, const std::string& path, verification_key_type* vk_out = nullptr) {
             b2g16::context& c = b2g16::context::instance();
             b2g16_params* p = nullptr;
@@ -315,9 +316,9 @@ template <class CurveType> struct r1cs_gg_ppzksnark {
                 throw b2g16::error(B2G16_E_INVALID_ARG, path + ": parameters of another circuit (l / h / ic lengths)");
             b2g16_r1cs_view rv = cs.view();
             std::vector<std::uint8_t> store[3], dens(nv);
-            auto dense = [&](const std::uint8_t* q, std::uint64_t n, const b2g16_csr& m, std::size_t w, std::vector<std::uint8_t>& s) {
+            auto dense = [&](const std::uint8_t* q, std::uint64_t n, const b2g16_csr& m, std::uint64_t n_always, std::size_t w, std::vector<std::uint8_t>& s) {
                 if (n == nv) return q;
-                if (b2g16_csr_density(&m, nv, dens.data(), nullptr) != B2G16_OK) throw b2g16::error(B2G16_E_INVALID_ARG, "constraint system: column out of range");
+                if (b2g16_query_density(&m, nv, n_always, dens.data(), nullptr) != B2G16_OK) throw b2g16::error(B2G16_E_INVALID_ARG, "constraint system: column out of range");
                 s.resize(nv * w);
                 if (b2g16_query_expand(q, n, dens.data(), nv, w, s.data()) != B2G16_OK)
                     throw b2g16::error(B2G16_E_INVALID_ARG, path + ": filtered query does not match the constraint system's density");
@@ -325,9 +326,9 @@ template <class CurveType> struct r1cs_gg_ppzksnark {
             };
             b2g16_pk_view v;
             v.alpha_g1 = p->alpha_g1; v.beta_g1 = p->beta_g1; v.delta_g1 = p->delta_g1; v.beta_g2 = p->beta_g2; v.delta_g2 = p->delta_g2;
-            v.a = dense(p->a, p->n_a, rv.A, 96, store[0]);
-            v.b_g1 = dense(p->b_g1, p->n_b_g1, rv.B, 96, store[1]);
-            v.b_g2 = dense(p->b_g2, p->n_b_g2, rv.B, 192, store[2]);
+            v.a = dense(p->a, p->n_a, rv.A, cs.n_in + 1, 96, store[0]);      // ONE and the inputs are always in the a query
+            v.b_g1 = dense(p->b_g1, p->n_b_g1, rv.B, 0, 96, store[1]);
+            v.b_g2 = dense(p->b_g2, p->n_b_g2, rv.B, 0, 192, store[2]);
             v.l = p->l; v.h = p->h; v.cs = &rv;
             b2g16_pk* pk = nullptr;
             c.check(b2g16_pk_load(c.get(), &v, &pk));

@@ -61,6 +61,23 @@ def test_vk_prepare_rejects_bad_key(ctx):
     vk[672 + 5] ^= 1                                                          # an IC point off the curve
     with pytest.raises(lib.B2g16Error):
         ctx.vk_prepare(vk)
+    # an IC point on the curve but outside the order-r subgroup (bellman's VerifyingKey::read checks this)
+    from oracle.pyref import bls12_381 as ref
+    from b2g16 import codec
+    for x in range(1, 200):
+        y = ref.fq_sqrt((x**3 + 4) % ref.P)
+        if y is not None and ref.pt_mul(ref.FQ, (x, y), ref.R) is not None:
+            break
+    vk = _golden_vk(g).copy()
+    vk[672 + 96:672 + 192] = codec.g1_from_points([(x, y)])[0]
+    with pytest.raises(lib.B2g16Error) as e:
+        ctx.vk_prepare(vk)
+    assert e.value.code == -3 and "subgroup" in str(e.value)
+    # a proof holding the point at infinity is a reject, not an error and not an accept
+    pvk = ctx.vk_prepare(_golden_vk(g))
+    inf_c = g["proof"].tobytes()[:144] + bytes([0xC0]) + bytes(47)
+    assert not ctx.verify(pvk, g["z"][1:1 + int(g["n_in"])], inf_c)
+    pvk.free()
 
 
 def test_prove_verify_batch(ctx, oracle):

@@ -55,8 +55,12 @@ def test_proof_codec_generators_and_infinity():
     assert enc[:48] == ref.g1_compress(ref.G1_GEN) and enc[48:144] == ref.g2_compress(ref.G2_GEN)
     assert enc[:4].hex() == "97f1d3a7" and enc[48:52].hex() == "93e02b60"
     assert enc[144] == 0xC0 and not any(enc[145:])
-    a, b, c = lib.proof_decode(enc)
-    assert np.array_equal(a, g1) and np.array_equal(b, g2) and not c.any()
+    # the encoder knows the point at infinity (0xC0, zeros), but a *proof* holding it is refused, as bellman's
+    # Proof::read refuses it: decode validates proofs, not arbitrary points
+    with pytest.raises(lib.B2g16Error):
+        lib.proof_decode(enc)
+    a, b, c = lib.proof_decode(lib.proof_encode(g1, g2, g1))
+    assert np.array_equal(a, g1) and np.array_equal(b, g2) and np.array_equal(c, g1)
     # negated point flips the sort flag only
     neg = codec.g1_from_points([ref.g1_neg(ref.G1_GEN)])[0]
     enc2 = lib.proof_encode(neg, g2, g1)
@@ -146,8 +150,8 @@ def test_density_filtered_queries():
     g = util.golden("groth16_m4")
     s = synth.SynthR1cs(int(g["log_m"]), int(g["n_in"]), int(g["seed"]), n_free=int(g["n_free"]))
     n_vars = g["a"].shape[0]
-    for mat, names in ((s.A, (("a", 96),)), (s.B, (("b_g1", 96), ("b_g2", 192)))):
-        dens, cnt = lib.csr_density(mat[1], n_vars)
+    for mat, n_always, names in ((s.A, s.n_in + 1, (("a", 96),)), (s.B, 0, (("b_g1", 96), ("b_g2", 192)))):
+        dens, cnt = lib.csr_density(mat[1], n_vars, n_always)
         assert cnt == int(dens.sum())
         for n, w in names:
             assert np.array_equal(dens, g[n].any(axis=1).astype(np.uint8)), n
@@ -170,3 +174,33 @@ def test_density_filtered_queries():
     ones, out = np.ones(3, np.uint8), np.zeros(3 * 192, np.uint8)
     rc = lib.load().b2g16_query_expand(lib._p(full), C.c_uint64(3), lib._p(ones), C.c_uint64(3), C.c_size_t(100), lib._p(out))
     assert rc == -1                                                          # not a point size
+
+
+def test_density_of_a_query_keeps_inputs_absent_from_A(oracle):
+    """a public input that occurs only in C (pack_into_inputs-style) has no entry in any row of A, yet its
+    `a` point is not the identity: the input-consistency row n_cons + j contributes L_{n_cons+j}(tau) to u_j (SURVEY
+    App. B step 2), and bellman keeps every input in the a query.  Plain column occupancy of A would drop it and
+    then refuse the (correct) filtered file; b2g16_query_density(A, n_always = n_in + 1) must not."""
+    from b2g16 import synth
+    s = synth.SynthR1cs(5, 3, 77, n_free=4)
+    acol = s.A[1].copy()
+    acol[acol == 2] = 0                                       # input 2 no longer occurs in A
+    bcol = s.B[1].copy()
+    bcol[bcol == 2] = 0
+    s.A = (s.A[0], acol, s.A[2]); s.B = (s.B[0], bcol, s.B[2])
+    cs = util.oracle_cs(oracle, s)
+    toxic, _, _ = util.toxic_from_seed(77)
+    key = oracle.groth16_setup(cs, toxic)
+    assert key.a[2].any(), "input-consistency row: the a point of an input is never the identity"
+    assert not key.b_g1[2].any()
+    plain, cnt_plain = lib.csr_density(acol, s.n_vars)
+    dens, cnt = lib.csr_density(acol, s.n_vars, s.n_in + 1)
+    assert plain[2] == 0 and dens[2] == 1 and cnt == cnt_plain + 1
+    filt, dens_file = lib.query_filter(key.a, 96)
+    assert np.array_equal(dens_file, dens) and filt.shape[0] == cnt
+    assert np.array_equal(lib.query_expand(filt, dens, 96), key.a)
+    with pytest.raises(lib.B2g16Error):
+        lib.query_expand(filt, plain, 96)                     # what round 1 did: refuses a correct file
+    dens_b, cnt_b = lib.csr_density(bcol, s.n_vars, 0)
+    filt_b, dens_b_file = lib.query_filter(key.b_g1, 96)
+    assert np.array_equal(dens_b_file, dens_b) and filt_b.shape[0] == cnt_b
