@@ -309,6 +309,43 @@ template <class PR> struct alignas(16) Fp {
         }
         return pow_limbs(e, N);
     }
+    // Inverse by the binary extended Euclidean algorithm on the limbs: ~2 log2(p) halvings and log2(p) subtractions of
+    // N-limb integers instead of the ~1.5 log2(p) full products of the Fermat ladder -- about ten times shorter as a
+    // *serial* chain, which is what matters where one thread inverts the product of a whole batch (msm_tree.cuh).
+    // Invariant: x1 * a == u, x2 * a == v (mod p).  inv(0) = 0.
+    B2_HD Fp inv_gcd() const {
+        if (is_zero()) return zero();
+        uint32_t u[N], w[N];
+        Fp x1 = zero(), x2 = zero();
+        x1.v[0] = 1;
+        for (int i = 0; i < N; ++i) { u[i] = v[i]; w[i] = PR::P(i); }
+        auto is_one = [](const uint32_t* t) { uint32_t r = t[0] ^ 1u; for (int i = 1; i < N; ++i) r |= t[i]; return r == 0; };
+        auto shr1 = [](uint32_t* t, uint32_t top) { for (int i = 0; i < N - 1; ++i) t[i] = (t[i] >> 1) | (t[i + 1] << 31); t[N - 1] = (t[N - 1] >> 1) | (top << 31); };
+        auto halve_mod = [&](Fp& x) {                    // x / 2 mod p for x in [0, p)
+            uint32_t top = 0;
+            if (x.v[0] & 1u) {
+                x.v[0] = ptx::add_cc(x.v[0], PR::P(0));
+                for (int i = 1; i < N; ++i) x.v[i] = ptx::addc_cc(x.v[i], PR::P(i));
+                top = ptx::addc(0, 0);
+            }
+            shr1(x.v, top);
+        };
+        auto geq = [](const uint32_t* a, const uint32_t* b) { for (int i = N - 1; i >= 0; --i) if (a[i] != b[i]) return a[i] > b[i]; return true; };
+        auto sub_n = [](uint32_t* a, const uint32_t* b) {  // a -= b, a >= b
+            a[0] = ptx::sub_cc(a[0], b[0]);
+            for (int i = 1; i < N - 1; ++i) a[i] = ptx::subc_cc(a[i], b[i]);
+            a[N - 1] = ptx::subc(a[N - 1], b[N - 1]);
+        };
+        while (!is_one(u) && !is_one(w)) {
+            while (!(u[0] & 1u)) { shr1(u, 0); halve_mod(x1); }
+            while (!(w[0] & 1u)) { shr1(w, 0); halve_mod(x2); }
+            if (geq(u, w)) { sub_n(u, w); x1 = x1 - x2; }
+            else { sub_n(w, u); x2 = x2 - x1; }
+        }
+        // y = (a R)^-1 as a plain residue; a^-1 R = y R^2: two Montgomery products with R^2
+        const Fp y = is_one(u) ? x1 : x2;
+        return (y * r2()) * r2();
+    }
 };
 
 typedef Fp<FrParams> Fr;
@@ -342,6 +379,10 @@ struct Fq2 {
     B2_HD Fq2 sqr() const;
     B2_HD Fq2 inv() const {
         Fq n = (c0.sqr() + c1.sqr()).inv();
+        return {c0 * n, (c1 * n).neg()};
+    }
+    B2_HD Fq2 inv_gcd() const {
+        Fq n = (c0.sqr() + c1.sqr()).inv_gcd();
         return {c0 * n, (c1 * n).neg()};
     }
 };

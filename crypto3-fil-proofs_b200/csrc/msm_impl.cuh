@@ -21,6 +21,7 @@
 #include "common.cuh"
 #include <cstdlib>
 #include "msm_digits.cuh"
+#include "msm_tree.cuh"
 
 namespace b2 {
 
@@ -72,14 +73,16 @@ static __global__ void msm_scatter_kernel(const uint32_t* __restrict__ scalars, 
 }
 // ---- 2. scans (uint32, exclusive, with the total appended at out[n]) -----------------
 constexpr int SCAN_BLOCK = 1024, SCAN_ITEMS = 8, SCAN_TILE = SCAN_BLOCK * SCAN_ITEMS;
-// mode 0: out = in ; mode 1: out = ceil(in / seg)
+// mode 0: out = in ; mode 1: out = ceil(in / seg) ; mode 2: `in` is an offsets array (n + 1 entries), out = scan of
+// ceil((in[i+1] - in[i]) / 2) -- the entry counts of the next level of the pairwise tree (msm_tree.cuh)
 static __global__ void __launch_bounds__(SCAN_BLOCK) scan_tile_kernel(const uint32_t* in, uint32_t* out, uint32_t* tile_sums, size_t n, int mode, uint32_t seg) {
     __shared__ uint32_t warp_sums[32];
     const size_t base = (size_t)blockIdx.x * SCAN_TILE + (size_t)threadIdx.x * SCAN_ITEMS;
     uint32_t v[SCAN_ITEMS], sum = 0;
 #pragma unroll
     for (int k = 0; k < SCAN_ITEMS; ++k) {
-        uint32_t x = (base + k < n) ? in[base + k] : 0u;
+        uint32_t x = 0u;
+        if (base + k < n) x = mode == 2 ? (in[base + k + 1] - in[base + k] + 1) / 2 : in[base + k];
         if (mode == 1) x = (x + seg - 1) / seg;
         v[k] = sum; sum += x;
     }
@@ -203,7 +206,15 @@ msm_accumulate_kernel(const Affine<F>* __restrict__ bases, const uint32_t* __res
 // continuations, at the start of later chunks) that msm_fix_pieces_kernel folds afterwards.
 constexpr uint32_t NO_BUCKET = 0xffffffffu;
 
-template <class F, int THREADS, int MINB> __global__ void __launch_bounds__(THREADS, MINB)
+// DIRECT: the entries are the points themselves (bases[e], the output of the affine tree levels, identities possible)
+// instead of (index, sign) references into the key.
+template <class F, bool DIRECT> B2_D Affine<F> chunk_entry_point(const Affine<F>* __restrict__ bases, uint32_t ix, uint32_t e) {
+    if (DIRECT) return load_affine(bases + e);
+    Affine<F> p = load_affine(bases + (ix & 0x7fffffffu));
+    if (ix >> 31) p.y = p.y.neg();
+    return p;
+}
+template <class F, int THREADS, int MINB, bool DIRECT = false> __global__ void __launch_bounds__(THREADS, MINB)
 msm_accumulate_chunked_kernel(const Affine<F>* __restrict__ bases, const uint32_t* __restrict__ sorted, const uint32_t* __restrict__ off,
                               uint32_t n_buckets, Xyzz<F>* __restrict__ bucket_acc, Xyzz<F>* __restrict__ head_part, Xyzz<F>* __restrict__ tail_part,
                               uint32_t* __restrict__ head_bucket, uint32_t* __restrict__ tail_bucket) {
@@ -222,17 +233,16 @@ msm_accumulate_chunked_kernel(const Affine<F>* __restrict__ bases, const uint32_
         bool head_open = off[b] < begin;                 // first bucket started in an earlier chunk
         Xyzz<F> acc = Xyzz<F>::identity();
         uint32_t e = begin;
-        uint32_t ix = sorted[e];
+        uint32_t ix = DIRECT ? 0u : sorted[e];
         while (e < end) {
             if (e == next) {                             // bucket b is complete: flush, move on
                 if (head_open) { head_part[tid] = acc; hb = b; head_open = false; } else bucket_acc[b] = acc;
                 acc = Xyzz<F>::identity();
                 do { ++b; next = off[b + 1]; } while (next == e);
             }
-            Affine<F> p = load_affine(bases + (ix & 0x7fffffffu));
-            if (ix >> 31) p.y = p.y.neg();
+            Affine<F> p = chunk_entry_point<F, DIRECT>(bases, ix, e);
             ++e;
-            if (e < end) {
+            if (!DIRECT && e < end) {
                 ix = sorted[e];
                 const char* q = reinterpret_cast<const char*>(bases + (ix & 0x7fffffffu));
                 prefetch_l2(q); prefetch_l2(q + sizeof(Affine<F>) - 4);
@@ -242,10 +252,9 @@ msm_accumulate_chunked_kernel(const Affine<F>* __restrict__ bases, const uint32_
                 // inside this chunk, fall through to add the next one in the same trip
                 acc.X = p.x; acc.Y = p.y; acc.ZZ = F::one(); acc.ZZZ = F::one();
                 if (e >= end || e == next) continue;
-                p = load_affine(bases + (ix & 0x7fffffffu));
-                if (ix >> 31) p.y = p.y.neg();
+                p = chunk_entry_point<F, DIRECT>(bases, ix, e);
                 ++e;
-                if (e < end) {
+                if (!DIRECT && e < end) {
                     ix = sorted[e];
                     const char* q = reinterpret_cast<const char*>(bases + (ix & 0x7fffffffu));
                     prefetch_l2(q); prefetch_l2(q + sizeof(Affine<F>) - 4);
@@ -536,14 +545,25 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
     const size_t max_segs = nb + max_entries / S + 1;
     const int n_tiles = (int)((nb + SCAN_TILE - 1) / SCAN_TILE);
 
+    // Levels of the batched-affine pairwise tree that run before the XYZZ accumulate (msm_tree.cuh): each level halves
+    // the entries of every bucket at ~6 field products per addition instead of 10; stop when ~4 entries per bucket are
+    // left (the tail levels would be launch- and inversion-latency bound).  B2G16_TREE_LEVELS / "tree_levels": -1 = by
+    // mean bucket occupancy, 0 = off.
+    int tree_levels = ctx->tree_levels;
+    if (tree_levels < 0) {
+        tree_levels = 0;
+        for (uint32_t m = mean; m >= 8; m >>= 1) ++tree_levels;
+    }
+    if (tree_levels > 12) tree_levels = 12;
     // G2 at 16-bit windows: the one-thread-per-bucket kernel is faster (measured 86 vs 99 ms at 2^22)
-    const bool chunked = ctx->acc_variant >= 100 && !(sizeof(F) > 48 && c <= 16);
+    const bool chunked = (ctx->acc_variant >= 100 && !(sizeof(F) > 48 && c <= 16)) || tree_levels > 0;
     // chunked-accumulate launch shape (threads per CTA, CTAs per SM).  G1 at 194 registers per thread: 2 x 160
     // threads = 10 warps per SM is the most that fits the register file without spilling (variant 105);
     // 101..104 = 128-thread CTAs, 1..4 per SM; 106 = 3 x 96.  G2: 64-thread CTAs at the 255-register cap, 4 per SM.
     int ch_threads = 0, ch_minb = 0;
     if (chunked) {
         if (sizeof(F) > 48) { ch_threads = 64; ch_minb = 4; }
+        else if (ctx->acc_variant < 100 || tree_levels > 0) { ch_threads = 128; ch_minb = 2; }
         else if (ctx->acc_variant == 105) { ch_threads = 160; ch_minb = 2; }
         else if (ctx->acc_variant == 106) { ch_threads = 96; ch_minb = 3; }
         else { ch_threads = 128; ch_minb = ctx->acc_variant - 100; }
@@ -585,8 +605,78 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
         B2_CUDA(cudaMemsetAsync(seg_acc.get(), 0, nb * sizeof(Xyzz<F>), st));            // empty bucket = identity (ZZ = 0)
         Xyzz<F>* head = pieces.get(); Xyzz<F>* tail = pieces.get() + n_chunks;
         uint32_t* hb = piece_bucket.get(); uint32_t* tb = piece_bucket.get() + n_chunks;
-#define B2_CH(THREADS, MINB) msm_accumulate_chunked_kernel<F, THREADS, MINB><<<148 * MINB, THREADS, 0, st>>>(d_bases, sorted.get(), off.get(), (uint32_t)nb, seg_acc.get(), head, tail, hb, tb)
         if (kl.e0) B2_CUDA(cudaEventRecord(kl.e0, st));
+        if (tree_levels > 0) {
+            // ---- affine tree levels, then the XYZZ accumulate over what is left; windows in groups that fit the memory
+            const uint32_t K = ctx->tree_k, K2 = 32;
+            auto caps = [&](size_t entries, uint32_t nbg, size_t* cap /*levels*/) {
+                size_t e = entries;
+                for (int l = 0; l < tree_levels; ++l) { e = (e + nbg) / 2 + 1; cap[l] = e; }
+            };
+            auto group_bytes = [&](int wg) {
+                size_t cap[16]; caps(n * (size_t)wg, (uint32_t)wg * B, cap);
+                const size_t c0 = cap[0], c1 = tree_levels > 1 ? cap[1] : 0;
+                return c0 * (sizeof(Affine<F>) + sizeof(F)) + c1 * sizeof(Affine<F>) + 3 * (c0 / K + 64) * sizeof(F) + 2 * ((size_t)wg * B + 1) * sizeof(uint32_t);
+            };
+            size_t free_b = 0, total_b = 0;
+            B2_CUDA(cudaMemGetInfo(&free_b, &total_b));
+            cudaMemPool_t pool; uint64_t reserved = 0, used = 0;
+            B2_CUDA(cudaDeviceGetDefaultMemPool(&pool, ctx->device));
+            B2_CUDA(cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReservedMemCurrent, &reserved));
+            B2_CUDA(cudaMemPoolGetAttribute(pool, cudaMemPoolAttrUsedMemCurrent, &used));
+            const size_t avail = (size_t)((free_b + (reserved - used)) * 0.85);
+            int wg = W;
+            while (wg > 1 && group_bytes(wg) > avail) wg = (wg + 1) / 2;
+            if (ctx->tree_wgroup > 0 && ctx->tree_wgroup < wg) wg = ctx->tree_wgroup;
+            const uint32_t nbg_max = (uint32_t)wg * B;
+            size_t cap[16]; caps(n * (size_t)wg, nbg_max, cap);
+            DevBuf<Affine<F>> ptsA(cap[0], st), ptsB(tree_levels > 1 ? cap[1] : 0, st);
+            DevBuf<F> pp0(cap[0], st);
+            DevBuf<uint32_t> offA((size_t)nbg_max + 1, st), offB((size_t)nbg_max + 1, st);
+            // product tree over the thread totals: depth d holds count_at(cap0, d) values
+            int depth_top = 1;
+            while (tree_count_at((uint32_t)cap[0], depth_top, K, K2) > TREE_TOP) ++depth_top;
+            std::vector<DevBuf<F>> val(depth_top + 1), ppd(depth_top + 1);
+            for (int d = 1; d <= depth_top; ++d) {
+                val[d].alloc(tree_count_at((uint32_t)cap[0], d, K, K2) + 1, st);
+                if (d < depth_top) ppd[d].alloc(tree_count_at((uint32_t)cap[0], d, K, K2) + 1, st);
+            }
+            DevBuf<F> top_scratch(TREE_TOP, st);
+            for (int w0 = 0; w0 < W; w0 += wg) {
+                const int w1 = w0 + wg < W ? w0 + wg : W;
+                const uint32_t nbg = (uint32_t)(w1 - w0) * B, b0 = (uint32_t)w0 * B;
+                caps(n * (size_t)(w1 - w0), nbg, cap);
+                TreeIn<F> in{d_bases, sorted.get(), nullptr, off.get() + b0};
+                for (int l = 0; l < tree_levels; ++l) {
+                    uint32_t* off_o = (l & 1) ? offB.get() : offA.get();
+                    Affine<F>* pts_o = (l & 1) ? ptsB.get() : ptsA.get();
+                    scan_u32(ctx, st, in.off, off_o, nbg, 2, 2, tile_sums.get());
+                    const uint32_t* e_out = off_o + nbg;
+                    const uint32_t t1 = tree_count_at((uint32_t)cap[l], 1, K, K2);
+                    tree_up0_kernel<F><<<(t1 + 127) / 128, 128, 0, st>>>(in, off_o, nbg, K, pp0.get(), val[1].get());
+                    int dt = 1;
+                    while (tree_count_at((uint32_t)cap[l], dt, K, K2) > TREE_TOP) {
+                        const uint32_t tn = tree_count_at((uint32_t)cap[l], dt + 1, K, K2);
+                        tree_up_kernel<F><<<(tn + 127) / 128, 128, 0, st>>>(val[dt].get(), e_out, dt, K, K2, ppd[dt].get(), val[dt + 1].get());
+                        ++dt;
+                    }
+                    tree_top_kernel<F><<<1, 32, 0, st>>>(val[dt].get(), e_out, dt, K, K2, top_scratch.get());
+                    for (int d = dt - 1; d >= 1; --d) {
+                        const uint32_t tn = tree_count_at((uint32_t)cap[l], d + 1, K, K2);
+                        tree_down_kernel<F><<<(tn + 127) / 128, 128, 0, st>>>(val[d].get(), e_out, d, K, K2, ppd[d].get(), val[d + 1].get());
+                    }
+                    tree_down0_kernel<F><<<(t1 + 127) / 128, 128, 0, st>>>(in, off_o, nbg, K, pp0.get(), val[1].get(), pts_o);
+                    ctx->launches += 3 + 2 * (dt - 1);
+                    in = TreeIn<F>{nullptr, nullptr, pts_o, off_o};
+                }
+                if (sizeof(F) > 48) msm_accumulate_chunked_kernel<F, 64, 4, true><<<148 * 4, 64, 0, st>>>(in.pts, nullptr, in.off, nbg, seg_acc.get() + b0, head, tail, hb, tb);
+                else msm_accumulate_chunked_kernel<F, 128, 2, true><<<148 * 2, 128, 0, st>>>(in.pts, nullptr, in.off, nbg, seg_acc.get() + b0, head, tail, hb, tb);
+                msm_fix_pieces_kernel<F><<<grid_for((size_t)n_chunks * 32, 128, 148 * 16), 128, 0, st>>>(seg_acc.get() + b0, head, tail, hb, tb, n_chunks);
+                ctx->launches += 2;
+            }
+            if (kl.e1) B2_CUDA(cudaEventRecord(kl.e1, st));
+        } else {
+#define B2_CH(THREADS, MINB) msm_accumulate_chunked_kernel<F, THREADS, MINB><<<148 * MINB, THREADS, 0, st>>>(d_bases, sorted.get(), off.get(), (uint32_t)nb, seg_acc.get(), head, tail, hb, tb)
         if (sizeof(F) > 48) B2_CH(64, 4);
         else switch (ctx->acc_variant) {
             case 101: B2_CH(128, 1); break;
@@ -601,6 +691,7 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
         if (kl.e1) B2_CUDA(cudaEventRecord(kl.e1, st));
         msm_fix_pieces_kernel<F><<<grid_for((size_t)n_chunks * 32, 128, 148 * 16), 128, 0, st>>>(seg_acc.get(), head, tail, hb, tb, n_chunks);
         ctx->launches += 2;
+        }
     } else {
         if (kl.e0) B2_CUDA(cudaEventRecord(kl.e0, st));
         launch_accumulate<F>(ctx, st, max_segs, d_bases, sorted.get(), hist.get(), off.get(), seg_off.get(), (uint32_t)nb, S, seg_acc.get());

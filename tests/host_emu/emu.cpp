@@ -15,7 +15,7 @@ template <class F> static int field_op(int op, const uint8_t* a, const uint8_t* 
         if (F::geq_p(la) || F::geq_p(lb)) return -2;
         F x = F::from_canonical(la), y = F::from_canonical(lb), r;
         switch (op) { case 0: r = x + y; break; case 1: r = x - y; break; case 2: r = x * y; break;
-            case 3: r = x.inv(); break; case 4: r = x.sqr(); break; default: r = x.neg(); }
+            case 3: r = x.inv(); break; case 4: r = x.sqr(); break; case 6: r = x.inv_gcd(); break; default: r = x.neg(); }
         r.to_canonical(lo); memcpy(out + B * i, lo, B);
     }
     return 0;
@@ -182,5 +182,87 @@ int emu_msm_g1(const uint8_t* bases, const uint8_t* scalars, size_t n, int c, ui
     for (int w = W - 2; w >= 0; --w) { for (int k = 0; k < c; ++k) acc = acc.dbl(); acc.add(win[w]); }
     store(acc.to_affine(), out);
     return 0;
+}
+}
+
+// ---------------------------------------------------------------------------------------
+// Batched-affine tree accumulation (msm_tree.cuh): the kernel bodies run thread by thread on the
+// CPU over the same sorted bucket layout the device builds, `levels` tree levels, then each
+// bucket's remaining entries are summed and the windows combined.  Checks the output <-> input
+// index arithmetic, the prefix-product / back-substitution chain across the depths of the product
+// tree and the special cases (copy, identity operand, doubling, cancellation) against the oracle.
+#include "msm_tree.cuh"
+template <class F, int SZ> static int emu_msm_tree(const uint8_t* bases, const uint8_t* scalars, size_t n, int c, uint32_t K, uint32_t K2, int levels, uint8_t* out) {
+    const int W = msm_windows(c);
+    const uint32_t B = 1u << (c - 1), nb = (uint32_t)W * B;
+    std::vector<Affine<F>> pts(n);
+    for (size_t i = 0; i < n; ++i) if (!load(pts[i], bases + SZ * i)) return -2;
+    std::vector<std::vector<uint32_t>> bucket(nb);
+    for (size_t i = 0; i < n; ++i) {
+        uint32_t s[8]; memcpy(s, scalars + 32 * i, 32);
+        if (pts[i].is_identity()) continue;
+        for (int w = 0; w < W; ++w) {
+            int d = msm_signed_digit(s, w, c);
+            if (d) bucket[(size_t)w * B + (uint32_t)((d < 0 ? -d : d) - 1)].push_back((uint32_t)i | (d < 0 ? 0x80000000u : 0u));
+        }
+    }
+    std::vector<uint32_t> sorted, off(nb + 1, 0);
+    for (uint32_t b = 0; b < nb; ++b) { off[b] = (uint32_t)sorted.size(); sorted.insert(sorted.end(), bucket[b].begin(), bucket[b].end()); }
+    off[nb] = (uint32_t)sorted.size();
+    TreeIn<F> in{pts.data(), sorted.data(), nullptr, off.data()};
+    std::vector<Affine<F>> cur, nxt;
+    std::vector<uint32_t> off_in = off, off_out(nb + 1);
+    for (int l = 0; l < levels; ++l) {
+        for (uint32_t b = 0, run = 0; b <= nb; ++b) { off_out[b] = run; if (b < nb) run += (off_in[b + 1] - off_in[b] + 1) / 2; }
+        const uint32_t e_out = off_out[nb];
+        nxt.assign(e_out, Affine<F>::identity());
+        // product tree: depth 0 = the denominators (implicit), depth d >= 1 = totals
+        std::vector<std::vector<F>> val, pp;
+        std::vector<F> pp0(e_out);
+        val.push_back(std::vector<F>(tree_count_at(e_out, 1, K, K2)));
+        in.off = off_in.data();
+        for (uint32_t t = 0; t < val[0].size() + 2; ++t) tree_up0_body<F>(in, off_out.data(), nb, K, t, pp0.data(), val[0].data());   // +2: threads past the end must do nothing
+        int depth = 1;
+        while (val.back().size() > TREE_TOP) {
+            const uint32_t cnt = (uint32_t)val.back().size();
+            if (cnt != tree_count_at(e_out, depth, K, K2)) return -5;
+            std::vector<F> tot((cnt + K2 - 1) / K2), p(cnt);
+            for (uint32_t t = 0; t < tot.size() + 2; ++t) tree_up_body<F>(val.back().data(), cnt, K2, t, p.data(), tot.data());
+            pp.push_back(p); val.push_back(tot); ++depth;
+        }
+        { std::vector<F> scratch(val.back().size() + 1); tree_top_body<F>(val.back().data(), (uint32_t)val.back().size(), scratch.data()); }
+        for (int d = (int)val.size() - 2; d >= 0; --d) {
+            const uint32_t cnt = (uint32_t)val[d].size();
+            for (uint32_t t = 0; t < val[d + 1].size() + 2; ++t) tree_down_body<F>(val[d].data(), cnt, K2, t, pp[d].data(), val[d + 1].data());
+        }
+        for (uint32_t t = 0; t < val[0].size() + 2; ++t) tree_down0_body<F>(in, off_out.data(), nb, K, t, pp0.data(), val[0].data(), nxt.data());
+        cur.swap(nxt);
+        off_in = off_out;
+        in = TreeIn<F>{nullptr, nullptr, cur.data(), off_in.data()};
+    }
+    in.off = off_in.data();
+    std::vector<Xyzz<F>> win(W);
+    for (int w = 0; w < W; ++w) {
+        Xyzz<F> run = Xyzz<F>::identity(), acc = Xyzz<F>::identity();
+        for (uint32_t j = B; j-- > 0;) {
+            const uint32_t b = (uint32_t)w * B + j;
+            Xyzz<F> bk = Xyzz<F>::identity();
+            for (uint32_t e = off_in[b]; e < off_in[b + 1]; ++e) bk.add_mixed(tree_entry(in, e));
+            run.add(bk);
+            acc.add(run);
+        }
+        win[w] = acc;
+    }
+    Xyzz<F> acc = win[W - 1];
+    for (int w = W - 2; w >= 0; --w) { for (int k = 0; k < c; ++k) acc = acc.dbl(); acc.add(win[w]); }
+    store(acc.to_affine(), out);
+    return 0;
+}
+extern "C" {
+int emu_msm_tree_g1(const uint8_t* bases, const uint8_t* scalars, size_t n, int c, uint32_t K, uint32_t K2, int levels, uint8_t* out) {
+    return emu_msm_tree<Fq, 96>(bases, scalars, n, c, K, K2, levels, out);
+}
+int emu_msm_tree_g2(const uint8_t* bases, const uint8_t* scalars, size_t n, int c, uint32_t K, uint32_t K2, int levels, uint8_t* out) {
+    return emu_msm_tree<Fq2, 192>(bases, scalars, n, c, K, K2, levels, out);
 }
 }

@@ -30,7 +30,7 @@ def _p(a):
     return a.ctypes.data_as(C.c_void_p)
 
 
-OPS = {"add": 0, "sub": 1, "mul": 2, "inv": 3, "sqr": 4, "neg": 5}
+OPS = {"add": 0, "sub": 1, "mul": 2, "inv": 3, "sqr": 4, "neg": 5, "inv_gcd": 6}
 
 
 def _op(emu, field, op, a, b=None):
@@ -202,3 +202,43 @@ def test_msm_pipeline_logic_vs_oracle(emu2, oracle, n, c, S):
     out = np.zeros(96, dtype=np.uint8)
     assert emu2.emu_msm_g1(_p(bases), _p(scal), C.c_size_t(n), c, C.c_uint32(S), _p(out)) == 0
     assert np.array_equal(out, oracle.msm_g1(bases, scal))
+
+
+@pytest.mark.parametrize("group,n,c,K,K2,levels", [(1, 1, 8, 4, 4, 2), (1, 37, 8, 3, 2, 3), (1, 300, 8, 2, 3, 4), (1, 300, 9, 16, 32, 9),
+                                                   (1, 2000, 8, 5, 7, 3), (2, 120, 8, 2, 3, 3)])
+def test_msm_tree_levels_vs_oracle(emu2, oracle, group, n, c, K, K2, levels):
+    """msm_tree.cuh kernel bodies (batched-affine pairwise tree, prefix-product tree of several depths, one
+    inversion per level) executed thread by thread on the CPU; result against the oracle's multiexp.  The edge
+    inputs put a doubling and a cancellation into single buckets, an identity base and zero / one / r-1 scalars."""
+    rng = np.random.Generator(np.random.PCG64(n * 131 + c + levels))
+    gen = oracle.g1_gen_mul if group == 1 else oracle.g2_gen_mul
+    bases = gen(codec.random_fr(n, rng))
+    scal = codec.random_fr(n, rng)
+    scal[0] = 0
+    if n > 12:
+        scal[1] = 0; scal[1, 0] = 1
+        scal[2] = np.frombuffer((codec.R_MOD - 1).to_bytes(32, "little"), dtype=np.uint8)
+        bases[3] = 0                                       # identity base
+        bases[4] = bases[5]; scal[4] = scal[5]             # equal points in every bucket they share -> doubling
+        bases[6] = bases[7]                                # P and -P in the same buckets -> the pair sums to the identity
+        scal[6] = codec.fr_from_ints([(codec.R_MOD - codec.fr_to_ints(scal[7:8])[0]) % codec.R_MOD])[0]
+        bases[8] = bases[9]; bases[10] = bases[9]; scal[8] = scal[9]; scal[10] = scal[9]    # three equal points: 2P then 2P + P
+    out = np.zeros(96 * group, dtype=np.uint8)
+    fn = emu2.emu_msm_tree_g1 if group == 1 else emu2.emu_msm_tree_g2
+    assert fn(_p(bases), _p(scal), C.c_size_t(n), c, C.c_uint32(K), C.c_uint32(K2), levels, _p(out)) == 0
+    want = oracle.msm_g1(bases, scal) if group == 1 else oracle.msm_g2(bases, scal)
+    assert np.array_equal(out, want)
+
+
+@pytest.mark.parametrize("field", ["fr", "fq"])
+def test_inverse_by_gcd_equals_fermat(emu, oracle, field):
+    """Fp::inv_gcd (binary extended Euclid on the limbs, used for the one inversion per tree level) against the
+    Fermat ladder and the oracle, with 0, 1, p - 1, 2 and a power of two among the inputs."""
+    rng = np.random.Generator(np.random.PCG64(99))
+    width = 32 if field == "fr" else 48
+    mod = codec.R_MOD if field == "fr" else 0x1a0111ea397fe69a4b1ba7b6434bacd764774b84f38512bf6730d2a0f6b0f6241eabfffeb153ffffb9feffffffffaaab
+    vals = [0, 1, 2, mod - 1, mod - 2, 1 << 200, (mod + 1) // 2] + [int.from_bytes(rng.bytes(width), "little") % mod for _ in range(150)]
+    a = np.stack([np.frombuffer(v.to_bytes(width, "little"), dtype=np.uint8) for v in vals])
+    got = _op(emu, field, "inv_gcd", a)
+    assert np.array_equal(got, _op(emu, field, "inv", a))
+    assert np.array_equal(got, oracle.field_op(field, "inv", a))
