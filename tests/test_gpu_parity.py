@@ -501,3 +501,49 @@ def test_fr_dot_device(ctx):
         da, db = torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda()
         want = sum(x * y for x, y in zip(codec.fr_to_ints(a), codec.fr_to_ints(b))) % codec.R_MOD
         assert codec.fr_to_ints(ctx.fr_dot_device(da.data_ptr(), db.data_ptr(), n).reshape(1, 32))[0] == want
+
+
+# ------------------------------------------- batched-affine tree accumulation (csrc/msm_tree.cuh)
+@pytest.mark.parametrize("group,n,c,levels,k,wgroup", [(1, 3000, 8, 1, 16, 0), (1, 3000, 8, 4, 2, 0), (1, 70000, 11, 5, 16, 3), (1, 70000, 13, 9, 7, 1),
+                                                        (1, 40000, 17, 3, 16, 0), (1, 20000, 20, 2, 16, 5), (2, 5000, 8, 4, 16, 0), (2, 5000, 9, 3, 5, 2),
+                                                        (2, 3000, 17, 2, 16, 0)])
+def test_msm_tree_levels_vs_oracle(ctx, oracle, group, n, c, levels, k, wgroup):
+    """Forced number of affine tree levels (more than the buckets need, too: a level over single-entry buckets is all
+    copies), outputs per thread and windows per pass, against the oracle with the edge inputs (doubling and cancellation
+    inside a bucket, identity base, zero / one / r - 1 scalars)."""
+    rng = np.random.Generator(np.random.PCG64(900 + 7 * c + levels + group))
+    bases, scal = _edge_inputs(oracle, n, rng, group)
+    bases[20] = bases[21]; bases[22] = bases[21]; scal[20] = scal[21]; scal[22] = scal[21]     # three equal points in each shared bucket
+    ctx.set_msm_window(c)
+    ctx.set_tuning("tree_levels", levels); ctx.set_tuning("tree_k", k); ctx.set_tuning("tree_wgroup", wgroup)
+    try:
+        if group == 1:
+            assert np.array_equal(ctx.msm_g1(bases, scal), oracle.msm_g1(bases, scal))
+        else:
+            assert np.array_equal(ctx.msm_g2(bases, scal), oracle.msm_g2(bases, scal))
+    finally:
+        ctx.set_msm_window(0)
+        ctx.set_tuning("tree_levels", -1); ctx.set_tuning("tree_k", 16); ctx.set_tuning("tree_wgroup", 0)
+
+
+def test_msm_tree_on_off_same_result_large(ctx):
+    """2^21 device-generated points, skewed (Filecoin-like) and uniform scalars: tree levels on (default) and off give the
+    same affine bytes -- the XYZZ-only path is the one parity-tested since round 1."""
+    import torch
+    n = 1 << 21
+    g = torch.Generator(device="cuda"); g.manual_seed(5)
+    k = torch.randint(0, 256, (n, 32), dtype=torch.uint8, device="cuda", generator=g); k[:, 31] &= 0x3F
+    s = torch.randint(0, 256, (n, 32), dtype=torch.uint8, device="cuda", generator=g); s[:, 31] &= 0x3F
+    u = torch.rand(n, device="cuda", generator=g)
+    sk = s.clone(); sk[u < 0.9, 2:] = 0; sk[u < 0.8] = 0; sk[(u >= 0.6) & (u < 0.8), 0] = 1
+    for group, cnt in ((1, n), (2, n // 8)):
+        bases = ctx.bases_generate(group, k.data_ptr(), cnt)
+        for sc in (s, sk):
+            got = ctx.msm_resident(bases, sc.data_ptr(), cnt)
+            ctx.set_tuning("tree_levels", 0)
+            try:
+                want = ctx.msm_resident(bases, sc.data_ptr(), cnt)
+            finally:
+                ctx.set_tuning("tree_levels", -1)
+            assert np.array_equal(got, want), group
+        bases.free()
