@@ -77,6 +77,9 @@ inline uint32_t mul_hi(uint32_t a, uint32_t b) { return (uint32_t)(((uint64_t)a 
 // (p, r from the BLS parameter; R, R^2, -p^-1 by big-int arithmetic).
 struct FrParams {
     static constexpr int N = 8;
+    // r = .. ffffffff 00000001: -r^-1 = -1 (mod 2^32), so the Montgomery quotient digit is m = -T[0], m * r[0] = m and
+    // m * r[1] = (m << 32) - m -- the two low limbs of every reduction row need no multiplier (mad_redc below)
+    static constexpr bool LOW_LIMBS_ARE_1_FFFFFFFF = true;
     // r = 0x73eda753299d7d483339d80809a1d80553bda402fffe5bfeffffffff00000001
     B2_HD static constexpr uint32_t P(int i) {
         constexpr uint32_t t[8] = {0x00000001u, 0xffffffffu, 0xfffe5bfeu, 0x53bda402u,
@@ -99,6 +102,7 @@ struct FrParams {
 };
 struct FqParams {
     static constexpr int N = 12;
+    static constexpr bool LOW_LIMBS_ARE_1_FFFFFFFF = false;
     // p = 0x1a0111ea397fe69a4b1ba7b6434bacd764774b84f38512bf6730d2a0f6b0f6241eabfffeb153ffffb9feffffffffaaab
     B2_HD static constexpr uint32_t P(int i) {
         constexpr uint32_t t[12] = {0xffffaaabu, 0xb9feffffu, 0xb153ffffu, 0x1eabfffeu, 0xf6b0f624u, 0x6730d2a0u,
@@ -248,9 +252,33 @@ template <class PR> struct alignas(16) Fp {
             mad_pairs(ev, a, bi);
             od[N - 1] = ptx::addc(od[N - 1], 0);
         }
-        // m is computed through an opaque mul.lo with `inv` read from constant memory:
-        // when ptxas can see m = -T[0] (Fr: inv = 2^32-1) it rewrites the reduction rows and
-        // stops pairing lo/hi into IMAD.WIDE (measured: 185 vs 137 FMA-pipe ops per Fr product).
+        if (PR::LOW_LIMBS_ARE_1_FFFFFFFF) {
+            // Fr: m = -T[0].  Row m * r added by hand for the limbs r[0] = 1 and r[1] = 2^32 - 1:
+            //   odd chain  (columns 1,2): + m * (2^32 - 1) = { lo = -m = T[0], hi = m - [m != 0] }
+            //   even chain (columns 0,1): + m            -> T[0] + m = 2^32 [m != 0]: only the carry [T[0] != 0] survives
+            // and six IMAD.WIDE.X for r[2..7] instead of eight + the mul.lo for m: 112 multiplier slots per product, not 136.
+            const uint32_t t0 = ev[0];
+            const uint32_t m = 0u - t0;
+            const uint32_t nz = t0 != 0u ? 1u : 0u;
+            od[0] = ptx::add_cc(od[0], t0);
+            od[1] = ptx::addc_cc(od[1], m - nz);
+#pragma unroll
+            for (int j = 2; j < N; j += 2) {
+                od[j] = ptx::madc_lo_cc(mod[j + 1], m, od[j]);
+                od[j + 1] = ptx::madc_hi_cc(mod[j + 1], m, od[j + 1]);
+            }
+            ev[0] = 0u;
+            ev[1] = ptx::add_cc(ev[1], nz);
+#pragma unroll
+            for (int j = 2; j < N; j += 2) {
+                ev[j] = ptx::madc_lo_cc(mod[j], m, ev[j]);
+                ev[j + 1] = ptx::madc_hi_cc(mod[j], m, ev[j + 1]);
+            }
+            od[N - 1] = ptx::addc(od[N - 1], 0);
+            return;
+        }
+        // m is computed through an opaque mul.lo with `inv` read from constant memory (a visible m = -T[0] lets ptxas
+        // rewrite the reduction rows into unpaired lo/hi products)
         const uint32_t m = ptx::mul_lo(ev[0], inv);
         mad_pairs(od, mod + 1, m);
         mad_pairs(ev, mod, m);

@@ -3,6 +3,7 @@
 // Replaces crypto3-math `evaluation_domain<Fr>` and zk `r1cs_to_qap::witness_map`
 // (un-vendored); called on behalf of compound_proof::circuit_proofs
 // (libs/storage/include/nil/filecoin/storage/proofs/core/proof/compound_proof.hpp:127-137).
+#include <cstdlib>
 #include "common.cuh"
 #include "ntt_plan.cuh"
 
@@ -15,6 +16,7 @@ struct NttDomain {
     Fr *glo_f = nullptr, *ghi_f = nullptr, *glo_i = nullptr, *ghi_i = nullptr;   // g^e, n^-1 g^-e
     Fr *glo_f_raw = nullptr, *glo_i_raw = nullptr;                                 // glo_* as plain residues
     Fr n_inv, zinv;                 // n^-1 ;  (g^n - 1)^-1
+    Fr* tw[NTT_MAX_PASSES] = {nullptr, nullptr, nullptr, nullptr};   // per strided pass: w_{2^L}^x, x < 2^(L-1) (ntt_stage_twiddle)
 };
 
 // out[e] = pre * base^(e << shift)
@@ -85,6 +87,23 @@ NttDomain* ntt_domain(Ctx* c, int log_n) {
     Fr raw_one = Fr::zero(); raw_one.v[0] = 1;
     d->glo_f_raw = make_table(c, g, raw_one, 0, n_lo);
     d->glo_i_raw = make_table(c, gi, d->n_inv * raw_one, 0, n_lo);
+    // Butterfly twiddle tables of the strided passes: 2^(L-1) entries each, i.e. n/2 for the first pass (2 GB at 2^27)
+    // and n/2^(k_0+1), .. for the later ones.  HBM streams them at a fraction of the time the multiplier would need to
+    // rebuild the twiddles (the transform is bound by the integer pipe, not by memory); when the allocation does not fit
+    // the pass keeps the two-level tlo * thi reconstruction.
+    if (!getenv("B2G16_NTT_NO_TW_TABLES")) {
+        for (int p = 0; p < d->plan.digits.n_pass; ++p) {
+            if (d->plan.contiguous[p]) continue;
+            const int L = d->plan.L[p];
+            const uint32_t count = 1u << (L - 1);
+            Fr* t = nullptr;
+            if (cudaMalloc((void**)&t, (size_t)count * sizeof(Fr)) != cudaSuccess) { cudaGetLastError(); continue; }
+            pow_table_kernel<<<grid_for(count, 256), 256, 0, c->stream>>>(t, host_root_of_unity(L), Fr::one(), 0, count);
+            c->launches++;
+            B2_CUDA(cudaGetLastError());
+            d->tw[p] = t;
+        }
+    }
     c->domains[log_n] = d;
     return d;
 }
@@ -94,6 +113,7 @@ void ntt_free_domains(Ctx* c) {
         NttDomain* d = kv.second;
         Fr* t[10] = {d->tlo_f, d->thi_f, d->tlo_i, d->thi_i, d->glo_f, d->ghi_f, d->glo_i, d->ghi_i, d->glo_f_raw, d->glo_i_raw};
         for (Fr* p : t) cudaFree(p);
+        for (Fr* p : d->tw) cudaFree(p);
         delete d;
     }
     c->domains.clear();
@@ -107,6 +127,8 @@ static NttTables tables(Ctx* c, const NttDomain* d, bool inverse) {
     t.tlo = inverse ? d->tlo_i : d->tlo_f; t.thi = inverse ? d->thi_i : d->thi_f;
     t.glo = inverse ? d->glo_i : d->glo_f; t.ghi = inverse ? d->ghi_i : d->ghi_f;
     t.glo_raw = inverse ? d->glo_i_raw : d->glo_f_raw;
+    for (int p = 0; p < NTT_MAX_PASSES; ++p) t.tw[p] = d->tw[p];
+    t.inverse = inverse ? 1 : 0;
     return t;
 }
 

@@ -52,7 +52,14 @@ B2_HD uint64_t ntt_digit_index(const NttDigits& d, uint64_t pos) {
 struct NttPass {
     int log_n, L, k, logc;      // block log-size, row bits, column bits of the tile
     int contiguous;             // 1: last pass (rows contiguous, columns = adjacent blocks)
-    int tw_mode;                // 0 none, 1 after small NTT (NR), 2 before (RN)
+    int tw_mode;                // 0 none, 1 after small NTT (NR), 2 before (RN): inter-pass twiddle rebuilt as tlo * thi (fallback);
+                                // 3: no inter-pass twiddle -- every butterfly of the pass takes its *combined* twiddle
+                                //    w_{2^L}^((j S + i2) << (k-1-hs)) from the table `tw` (see ntt_stage_twiddle)
+    int dit;                    // 1: decimation-in-time stages (rows bit-reversed on load, half-size ascending, twiddle before
+                                //    the butterfly): the transpose of the DIF pass, used by strided passes of RN transforms
+    const Fr* tw;               // tw_mode 3: w_{2^L}^x, x < 2^(L-1), forward roots; the inverse transform reads -tw[2^(L-1) - x]
+    uint32_t tw_half;           // 2^(L-1)
+    int tw_inv;                 // 1: inverse roots wanted
     int scale_mode;             // 0 none, 1 on load, 2 on store
     int scale_kind;             // 0: constant cscale; 1: g-power table at natural position;
                                 // 2: g-power table at digit-reversed index of the position
@@ -155,9 +162,31 @@ B2_HD void ntt_phase_load(const NttPass& p, const NttTile& t, const Fr* data, ui
     if (p.fuse_abc) x = (x * fr_load(p.src_b + g) - fr_load(p.src_c + g)) * p.zinv;
     if (p.scale_mode == 1) x = x * ntt_scale(p, g);
     if (p.tw_mode == 2 && row != 0) x = x * ntt_twiddle(p, t.col0 + col, (uint32_t)row);
-    fr_to_planes(x, s_lo[e], s_hi[e]);
+    const int dst = p.dit ? t.elem((int)bitrev_u32((uint32_t)row, p.k), col) : e;
+    fr_to_planes(x, s_lo[dst], s_hi[dst]);
 }
-// DIF butterfly `b` of the stage with half-size h = 2^hs
+// Twiddle of the butterfly (row j of the half-block, column col) in the stage with half-size h = 2^hs.
+// Contiguous pass / fallback modes: the pure root w_{2^(hs+1)}^j from the 2^11-th root table.
+// tw_mode 3 (strided pass of a block of 2^L positions, S = 2^(L-k) columns): the pass is the first k stages of the
+// radix-2 transform of the whole block, whose butterfly (q, q + h S), q = j S + i2, carries w_{2 h S}^q =
+// w_{2^L}^(q << (k-1-hs)); using it directly leaves nothing for an inter-pass twiddle -- one product per butterfly
+// and none per element, where the fallback pays 1-2 more products per element and pass.  `neg` is set when the
+// value returned is the negated twiddle (inverse roots: w^-x = -w^(2^(L-1) - x)); the caller folds the sign into
+// its add / sub.  Returns false when the twiddle is 1.
+B2_HD bool ntt_stage_twiddle(const NttPass& p, const NttTile& t, int hs, int j, int col, Fr& w, bool& neg) {
+    neg = false;
+    if (p.tw_mode == 3) {
+        const uint64_t x = ((((uint64_t)j) << (p.L - p.k)) + t.col0 + (uint64_t)col) << (p.k - 1 - hs);
+        if (x == 0) return false;
+        if (p.tw_inv) { w = fr_load(p.tw + (p.tw_half - x)); neg = true; }
+        else w = fr_load(p.tw + x);
+        return true;
+    }
+    if (j == 0) return false;
+    w = fr_load(p.roots + ((uint32_t)j << (NTT_ROOT_LOG - 1 - hs)));
+    return true;
+}
+// butterfly `b` of the stage with half-size h = 2^hs: DIF (u + v, (u - v) w) or, for p.dit, DIT (u + v w, u - v w)
 B2_HD void ntt_phase_stage(const NttPass& p, const NttTile& t, uint4* s_lo, uint4* s_hi, int hs, int b) {
     int half_rows = 1 << (p.k - 1);
     int rb, col;
@@ -169,14 +198,25 @@ B2_HD void ntt_phase_stage(const NttPass& p, const NttTile& t, uint4* s_lo, uint
     int e0 = t.elem(r0, col), e1 = t.elem(r0 + h, col);
     Fr u = fr_from_planes(s_lo[e0], s_hi[e0]);
     Fr v = fr_from_planes(s_lo[e1], s_hi[e1]);
-    Fr s = u + v, d = u - v;
-    if (j) d = d * fr_load(p.roots + ((uint32_t)j << (NTT_ROOT_LOG - 1 - hs)));
+    Fr w; bool neg;
+    const bool has_w = ntt_stage_twiddle(p, t, hs, j, col, w, neg);
+    Fr s, d;
+    if (p.dit) {
+        if (has_w) v = v * w;
+        if (neg) { s = u - v; d = u + v; } else { s = u + v; d = u - v; }
+    } else {
+        s = u + v;
+        d = neg ? v - u : u - v;
+        if (has_w) d = d * w;
+    }
     fr_to_planes(s, s_lo[e0], s_hi[e0]);
     fr_to_planes(d, s_lo[e1], s_hi[e1]);
 }
+// stage order: DIF runs half-sizes k-1 .. 0, DIT 0 .. k-1
+B2_HD int ntt_stage_hs(const NttPass& p, int i) { return p.dit ? i : p.k - 1 - i; }
 B2_HD void ntt_phase_store(const NttPass& p, const NttTile& t, Fr* data, const uint4* s_lo, const uint4* s_hi, int e) {
     int row = t.row_of(e), col = t.col_of(e);          // output row k1 (natural order)
-    int src = t.elem((int)bitrev_u32((uint32_t)row, p.k), col);
+    int src = p.dit ? e : t.elem((int)bitrev_u32((uint32_t)row, p.k), col);
     Fr x = fr_from_planes(s_lo[src], s_hi[src]);
     uint64_t g = t.gpos(row, col);
     if (p.tw_mode == 1 && row != 0) x = x * ntt_twiddle(p, t.col0 + col, (uint32_t)row);
@@ -195,7 +235,8 @@ static __global__ void __launch_bounds__(256) ntt_pass_kernel(const Fr* src, Fr*
         const NttTile t = ntt_make_tile(p, tile_id);
         for (int e = threadIdx.x; e < T; e += blockDim.x) ntt_phase_load(p, t, src, s_lo, s_hi, e);
         __syncthreads();
-        for (int hs = p.k - 1; hs >= 0; --hs) {
+        for (int i = 0; i < p.k; ++i) {
+            const int hs = ntt_stage_hs(p, i);
             for (int b = threadIdx.x; b < T / 2; b += blockDim.x) ntt_phase_stage(p, t, s_lo, s_hi, hs, b);
             __syncthreads();
         }

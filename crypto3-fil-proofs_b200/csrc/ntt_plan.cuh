@@ -56,6 +56,10 @@ struct NttTables {                    // device (or host-emulation) pointers, al
     const Fr* tlo; const Fr* thi;     // w_N^e two-level        (forward or inverse set)
     const Fr* glo; const Fr* ghi;     // coset powers two-level (g^e, or n^-1 * g^-e)
     const Fr* glo_raw;                // glo as plain (non-Montgomery) residues: a Montgomery product with it also leaves Montgomery form
+    // per strided pass p: w_{2^L_p}^x, x < 2^(L_p - 1) (always the FORWARD roots; an inverse transform reads them negated
+    // and mirrored), or null -> that pass rebuilds its inter-pass twiddles from tlo / thi (fallback when the table does not fit)
+    const Fr* tw[NTT_MAX_PASSES];
+    int inverse;                      // this set serves an inverse transform
 };
 
 // Passes of one transform in execution order.  rn = false: natural -> digit-reversed
@@ -69,6 +73,10 @@ inline std::vector<NttPass> ntt_build_passes(const NttPlan& pl, bool rn, const N
         q.log_n = pl.digits.log_n; q.L = pl.L[p]; q.k = pl.digits.k[p]; q.logc = pl.logc[p];
         q.contiguous = pl.contiguous[p];
         q.tw_mode = q.contiguous ? 0 : (rn ? 2 : 1);
+        q.dit = 0; q.tw = nullptr; q.tw_half = 0; q.tw_inv = 0;
+        if (!q.contiguous && tb.tw[p]) {                 // combined butterfly twiddles: no inter-pass twiddle product at all
+            q.tw_mode = 3; q.tw = tb.tw[p]; q.tw_half = 1u << (q.L - 1); q.tw_inv = tb.inverse; q.dit = rn ? 1 : 0;
+        }
         q.scale_mode = 0; q.scale_kind = 0;
         q.roots = tb.roots; q.tlo = tb.tlo; q.thi = tb.thi; q.lo_bits = pl.lo_bits;
         q.glo = tb.glo; q.ghi = tb.ghi; q.g_lo_bits = pl.lo_bits;

@@ -74,7 +74,8 @@ static std::vector<Fr> pow_table(Fr base, Fr pre, int shift, uint32_t count) {
 struct EmuDomain {
     NttPlan plan; NttConsts k;
     std::vector<Fr> roots_f, roots_i, tlo_f, thi_f, tlo_i, thi_i, glo_f, ghi_f, glo_i, ghi_i, glo_f_raw, glo_i_raw;
-    explicit EmuDomain(int log_n) {
+    std::vector<Fr> tw[NTT_MAX_PASSES];
+    explicit EmuDomain(int log_n, bool tw_tables = true) {
         plan = ntt_make_plan(log_n);
         int lo = plan.lo_bits, hi = log_n - lo;
         uint32_t n_lo = 1u << lo, n_hi = 1u << (hi > 0 ? hi : 0);
@@ -90,6 +91,7 @@ struct EmuDomain {
         glo_i = pow_table(gi, k.n_inv, 0, n_lo); ghi_i = pow_table(gi, Fr::one(), lo, n_hi);
         Fr raw_one = Fr::zero(); raw_one.v[0] = 1;
         glo_f_raw = pow_table(g, raw_one, 0, n_lo); glo_i_raw = pow_table(gi, k.n_inv * raw_one, 0, n_lo);
+        if (tw_tables) for (int p = 0; p < plan.digits.n_pass; ++p) if (!plan.contiguous[p]) tw[p] = pow_table(root_of_unity(plan.L[p]), Fr::one(), 0, 1u << (plan.L[p] - 1));
     }
     NttTables tables(bool inverse) const {
         NttTables t;
@@ -97,6 +99,8 @@ struct EmuDomain {
         t.tlo = (inverse ? tlo_i : tlo_f).data(); t.thi = (inverse ? thi_i : thi_f).data();
         t.glo = (inverse ? glo_i : glo_f).data(); t.ghi = (inverse ? ghi_i : ghi_f).data();
         t.glo_raw = (inverse ? glo_i_raw : glo_f_raw).data();
+        for (int p = 0; p < NTT_MAX_PASSES; ++p) t.tw[p] = tw[p].empty() ? nullptr : tw[p].data();
+        t.inverse = inverse ? 1 : 0;
         return t;
     }
 };
@@ -107,13 +111,15 @@ static void run_step(const NttStep& s) {
     for (uint64_t tile = 0; tile < ntt_pass_tiles(p); ++tile) {
         NttTile t = ntt_make_tile(p, tile);
         for (int e = 0; e < T; ++e) ntt_phase_load(p, t, s.src, lo.data(), hi.data(), e);
-        for (int hs = p.k - 1; hs >= 0; --hs) for (int b = 0; b < T / 2; ++b) ntt_phase_stage(p, t, lo.data(), hi.data(), hs, b);
+        for (int i = 0; i < p.k; ++i) for (int b = 0; b < T / 2; ++b) ntt_phase_stage(p, t, lo.data(), hi.data(), ntt_stage_hs(p, i), b);
         for (int e = 0; e < T; ++e) ntt_phase_store(p, t, s.dst, lo.data(), hi.data(), e);
     }
 }
 extern "C" {
+static bool g_emu_tw_tables = true;
+void emu_set_tw_tables(int on) { g_emu_tw_tables = on != 0; }
 int emu_ntt(uint8_t* data, unsigned log_n, int inverse, int coset) {
-    EmuDomain d((int)log_n);
+    EmuDomain d((int)log_n, g_emu_tw_tables);
     size_t n = (size_t)1 << log_n;
     std::vector<Fr> buf(n), tmp(n);
     memcpy(buf.data(), data, 32 * n);
@@ -122,7 +128,7 @@ int emu_ntt(uint8_t* data, unsigned log_n, int inverse, int coset) {
     return d.plan.digits.n_pass;
 }
 int emu_h_from_abc(const uint8_t* a, const uint8_t* b, const uint8_t* c, unsigned log_m, uint8_t* h) {
-    EmuDomain d((int)log_m);
+    EmuDomain d((int)log_m, g_emu_tw_tables);
     size_t m = (size_t)1 << log_m;
     std::vector<Fr> va(m), vb(m), vc(m), vh(m);
     memcpy(va.data(), a, 32 * m); memcpy(vb.data(), b, 32 * m); memcpy(vc.data(), c, 32 * m);

@@ -134,14 +134,32 @@ def emu2():
 
 @pytest.mark.parametrize("log_n", [0, 1, 2, 5, 11, 12, 13, 14])
 @pytest.mark.parametrize("inverse,coset", [(0, 0), (1, 0), (0, 1), (1, 1)])
-def test_ntt_passes_vs_oracle(emu2, oracle, log_n, inverse, coset):
+@pytest.mark.parametrize("tw_tables", [1, 0])
+def test_ntt_passes_vs_oracle(emu2, oracle, log_n, inverse, coset, tw_tables):
+    """tw_tables = 1: strided passes take combined butterfly twiddles from per-pass root tables (no inter-pass twiddle);
+    0: the fallback that rebuilds inter-pass twiddles as tlo * thi."""
+    if not tw_tables and log_n <= 11:
+        pytest.skip("single contiguous pass: no strided pass to differ")
     rng = np.random.Generator(np.random.PCG64(1000 + log_n))
     x = codec.random_fr(1 << log_n, rng)
     got = x.copy()
-    n_pass = emu2.emu_ntt(_p(got), C.c_uint(log_n), inverse, coset)
+    emu2.emu_set_tw_tables(tw_tables)
+    try:
+        n_pass = emu2.emu_ntt(_p(got), C.c_uint(log_n), inverse, coset)
+    finally:
+        emu2.emu_set_tw_tables(1)
     assert n_pass == (1 if log_n <= 11 else 2)
     want = oracle.ntt(x, inverse=bool(inverse), coset=bool(coset))
     assert np.array_equal(got, want)
+
+
+def test_ntt_three_passes_vs_oracle(emu2, oracle):
+    """2^21: the smallest domain with two strided passes (9 + 9 + 3 index bits), inverse coset transform."""
+    log_n = 21
+    x = codec.random_fr(1 << log_n, np.random.Generator(np.random.PCG64(21)))
+    got = x.copy()
+    assert emu2.emu_ntt(_p(got), C.c_uint(log_n), 1, 1) == 3
+    assert np.array_equal(got, oracle.ntt(x, inverse=True, coset=True))
 
 
 def test_ntt_golden(emu2):
