@@ -128,6 +128,28 @@ bool write_points(FILE* f, const uint8_t* abi, uint64_t n, int g2) {
 
 }  // namespace
 
+// The vk block that opens a .params file and is the whole of a .vk file (param_cache.cu):
+// alpha_g1 beta_g1 beta_g2 gamma_g2 delta_g1 delta_g2 u32_be n_ic ic[]
+namespace b2io {
+bool read_vk_block(FILE* f, b2g16_params* p, int* rc) {
+    uint8_t hdr[864];
+    if (fread(hdr, 1, sizeof hdr, f) != sizeof hdr) { *rc = B2G16_E_INVALID_ARG; return false; }
+    if (!(g1_file_to_abi(hdr, p->alpha_g1) && g1_file_to_abi(hdr + 96, p->beta_g1) && g2_file_to_abi(hdr + 192, p->beta_g2) &&
+          g2_file_to_abi(hdr + 384, p->gamma_g2) && g1_file_to_abi(hdr + 576, p->delta_g1) && g2_file_to_abi(hdr + 672, p->delta_g2))) {
+        *rc = B2G16_E_NOT_CANONICAL; return false;
+    }
+    if (!read_u32_be(f, &p->n_ic)) { *rc = B2G16_E_INVALID_ARG; return false; }
+    *rc = read_points(f, p->n_ic, 0, &p->ic);
+    return *rc == B2G16_OK;
+}
+bool write_vk_block(FILE* f, const b2g16_params* p) {
+    uint8_t hdr[864];
+    g1_abi_to_file(p->alpha_g1, hdr); g1_abi_to_file(p->beta_g1, hdr + 96); g2_abi_to_file(p->beta_g2, hdr + 192);
+    g2_abi_to_file(p->gamma_g2, hdr + 384); g1_abi_to_file(p->delta_g1, hdr + 576); g2_abi_to_file(p->delta_g2, hdr + 672);
+    return fwrite(hdr, 1, sizeof hdr, f) == sizeof hdr && write_u32_be(f, p->n_ic) && write_points(f, p->ic, p->n_ic, 0);
+}
+}  // namespace b2io
+
 extern "C" {
 
 int b2g16_params_free(b2g16_params* p) {
@@ -145,15 +167,11 @@ int b2g16_params_read(const char* path, b2g16_params** out) {
     b2g16_params* p = new (std::nothrow) b2g16_params();
     if (!p) return B2G16_E_OOM;
     memset(p, 0, sizeof *p);
-    uint8_t hdr[864];
     int rc = B2G16_OK;
-    if (fread(hdr, 1, sizeof hdr, fh.f) != sizeof hdr) rc = B2G16_E_INVALID_ARG;
-    if (rc == B2G16_OK && !(g1_file_to_abi(hdr, p->alpha_g1) && g1_file_to_abi(hdr + 96, p->beta_g1) && g2_file_to_abi(hdr + 192, p->beta_g2) &&
-                            g2_file_to_abi(hdr + 384, p->gamma_g2) && g1_file_to_abi(hdr + 576, p->delta_g1) && g2_file_to_abi(hdr + 672, p->delta_g2)))
-        rc = B2G16_E_NOT_CANONICAL;
-    struct { uint64_t* n; uint8_t** buf; int g2; } arr[6] = {{&p->n_ic, &p->ic, 0}, {&p->n_h, &p->h, 0}, {&p->n_l, &p->l, 0},
+    b2io::read_vk_block(fh.f, p, &rc);                   // header + IC points
+    struct { uint64_t* n; uint8_t** buf; int g2; } arr[5] = {{&p->n_h, &p->h, 0}, {&p->n_l, &p->l, 0},
                                                             {&p->n_a, &p->a, 0}, {&p->n_b_g1, &p->b_g1, 0}, {&p->n_b_g2, &p->b_g2, 1}};
-    for (int i = 0; i < 6 && rc == B2G16_OK; ++i) {
+    for (int i = 0; i < 5 && rc == B2G16_OK; ++i) {
         if (!read_u32_be(fh.f, arr[i].n)) { rc = B2G16_E_INVALID_ARG; break; }
         rc = read_points(fh.f, *arr[i].n, arr[i].g2, arr[i].buf);
     }
@@ -168,12 +186,9 @@ int b2g16_params_write(const char* path, const b2g16_params* p) {
     for (uint64_t n : counts) if (n >> 32) return B2G16_E_INVALID_ARG;   // u32 length prefixes
     File fh(path, "wb");
     if (!fh.f) return B2G16_E_INVALID_ARG;
-    uint8_t hdr[864];
-    g1_abi_to_file(p->alpha_g1, hdr); g1_abi_to_file(p->beta_g1, hdr + 96); g2_abi_to_file(p->beta_g2, hdr + 192);
-    g2_abi_to_file(p->gamma_g2, hdr + 384); g1_abi_to_file(p->delta_g1, hdr + 576); g2_abi_to_file(p->delta_g2, hdr + 672);
-    bool ok = fwrite(hdr, 1, sizeof hdr, fh.f) == sizeof hdr;
-    const uint8_t* bufs[6] = {p->ic, p->h, p->l, p->a, p->b_g1, p->b_g2};
-    for (int i = 0; i < 6 && ok; ++i) ok = write_u32_be(fh.f, counts[i]) && write_points(fh.f, bufs[i], counts[i], i == 5);
+    bool ok = b2io::write_vk_block(fh.f, p);
+    const uint8_t* bufs[5] = {p->h, p->l, p->a, p->b_g1, p->b_g2};
+    for (int i = 0; i < 5 && ok; ++i) ok = write_u32_be(fh.f, counts[i + 1]) && write_points(fh.f, bufs[i], counts[i + 1], i == 4);
     return ok ? B2G16_OK : B2G16_E_INTERNAL;
 }
 

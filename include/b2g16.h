@@ -269,6 +269,24 @@ int b2g16_query_expand(const uint8_t* filtered, uint64_t n_filtered, const uint8
 int b2g16_query_filter(const uint8_t* dense, uint64_t n_vars, size_t point_bytes, uint8_t* filtered_out, uint8_t* density_out,
                        uint64_t* count_out);
 
+/* ---- parameter-cache entries: the naming and the two small files of S/core/parameter_cache.hpp.
+ *   b2g16_cache_dir        : $FIL_PROOFS_PARAMETER_CACHE, else /var/tmp/filecoin-proof-parameters        (:52-53,65-71)
+ *   b2g16_cache_identifier : "<cache_prefix>-<hex sha256(parameter_set_identifier)>"                     (:166-173)
+ *   b2g16_cache_path       : "<dir>/v28-<identifier>.<ext>", kind 0 = params, 1 = vk, 2 = meta            (:50,54-56,73-94)
+ *   b2g16_meta_write/_read : cache_entry_metadata { sector_size } as {"sector_size":N}                   (:108-123)
+ *   b2g16_vk_file_write/_read : the verifying key alone, = the vk block that opens a .params file        (:131-145);
+ *                            read returns a b2g16_params with only the header and ic filled (free with b2g16_params_free)
+ * out / cap: caller's buffer for the NUL-terminated string; B2G16_E_INVALID_ARG if it does not fit.  Host-only. */
+#define B2G16_PARAMETER_CACHE_VERSION 28
+int b2g16_sha256(const uint8_t* data, size_t len, uint8_t out32[32]);
+int b2g16_cache_dir(char* out, size_t cap);
+int b2g16_cache_identifier(const char* cache_prefix, const char* parameter_set_identifier, char* out, size_t cap);
+int b2g16_cache_path(const char* identifier, int kind, char* out, size_t cap);
+int b2g16_meta_write(const char* path, uint64_t sector_size);
+int b2g16_meta_read(const char* path, uint64_t* sector_size);
+int b2g16_vk_file_write(const char* path, const b2g16_params*);
+int b2g16_vk_file_read(const char* path, b2g16_params** out);
+
 /* ---- synthetic-instance support (bench/test): evaluate one layer of a forward-built R1CS on
  *      the device: for rows [row0,row1): z[out_base + i] = (A_i . z) * (B_i . z).  d_z canonical. */
 int b2g16_synth_witness(b2g16_ctx*, const b2g16_pk*, uint8_t* d_assignment32, uint64_t n_free);
