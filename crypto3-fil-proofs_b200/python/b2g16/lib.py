@@ -85,6 +85,78 @@ def params_read(path):
     return out
 
 
+# ---- parameter-cache entries (S/core/parameter_cache.hpp:50-94,108-145,166-173) ----------------
+def _cstr(fn, *args):
+    buf = C.create_string_buffer(4096)
+    rc = fn(*args, buf, C.c_size_t(len(buf)))
+    if rc != 0:
+        raise B2g16Error(rc, fn.__name__)
+    return os.fsdecode(buf.value)
+
+
+def sha256(data):
+    out = (C.c_uint8 * 32)()
+    rc = load().b2g16_sha256(bytes(data), C.c_size_t(len(data)), out)
+    if rc != 0:
+        raise B2g16Error(rc, "b2g16_sha256")
+    return bytes(out)
+
+
+def cache_dir():
+    return _cstr(load().b2g16_cache_dir)
+
+
+def cache_identifier(cache_prefix, parameter_set_identifier):
+    return _cstr(load().b2g16_cache_identifier, os.fsencode(cache_prefix), os.fsencode(parameter_set_identifier))
+
+
+CACHE_PARAMS, CACHE_VK, CACHE_META = 0, 1, 2
+
+
+def cache_path(identifier, kind):
+    return _cstr(load().b2g16_cache_path, os.fsencode(identifier), C.c_int(kind))
+
+
+def meta_write(path, sector_size):
+    rc = load().b2g16_meta_write(os.fsencode(path), C.c_uint64(sector_size))
+    if rc != 0:
+        raise B2g16Error(rc, "b2g16_meta_write(%s)" % path)
+
+
+def meta_read(path):
+    v = C.c_uint64(0)
+    rc = load().b2g16_meta_read(os.fsencode(path), C.byref(v))
+    if rc != 0:
+        raise B2g16Error(rc, "b2g16_meta_read(%s)" % path)
+    return int(v.value)
+
+
+def vk_file_write(path, params):
+    """params: dict with the six single points and ic (ABI encodings), as for params_write."""
+    st = Params()
+    for n, w in PARAM_POINTS:
+        C.memmove(getattr(st, n), _p(_u8(params[n])), w)
+    ic = _u8(params["ic"], 96)
+    st.n_ic, st.ic = ic.shape[0], _p(ic)
+    rc = load().b2g16_vk_file_write(os.fsencode(path), C.byref(st))
+    if rc != 0:
+        raise B2g16Error(rc, "b2g16_vk_file_write(%s)" % path)
+
+
+def vk_file_read(path):
+    h = C.POINTER(Params)()
+    rc = load().b2g16_vk_file_read(os.fsencode(path), C.byref(h))
+    if rc != 0:
+        raise B2g16Error(rc, "b2g16_vk_file_read(%s)" % path)
+    st, out = h.contents, {}
+    for n, w in PARAM_POINTS:
+        out[n] = np.frombuffer(bytes(getattr(st, n)), dtype=np.uint8).copy()
+    cnt = int(st.n_ic)
+    out["ic"] = np.ctypeslib.as_array(C.cast(st.ic, C.POINTER(C.c_uint8)), shape=(cnt * 96,)).reshape(cnt, 96).copy() if cnt else np.zeros((0, 96), np.uint8)
+    load().b2g16_params_free(h)
+    return out
+
+
 def csr_density(col, n_vars, n_always=0):
     """b2g16_query_density: bitmap (uint8, n_vars) of the variables whose query point is present, given the matrix's CSR
     column indices; n_always = n_in + 1 for the a query (input-consistency rows), 0 for b_g1 / b_g2."""

@@ -1,0 +1,4 @@
+// Forwarding header: the include path crypto3-fil-proofs names (crypto3-algebra's multiexp entry point) resolves to the libb2g16 shim,
+// which declares the same nil::crypto3 names over the C ABI of include/b2g16.h.
+#pragma once
+#include <nil/crypto3/b2g16_shim.hpp>

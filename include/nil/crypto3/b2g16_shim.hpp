@@ -59,6 +59,37 @@ template <std::size_t N> struct bytes_value {
     static bytes_value zero() { return bytes_value(); }
 };
 
+
+// Cache entry names of S/core/parameter_cache.hpp:50-94,166-173 (v28-<prefix>-<sha256>.{params,vk,meta} under
+// $FIL_PROOFS_PARAMETER_CACHE) and the metadata file (:108-123).
+inline std::string cache_string(int (*fn)(const char*, int, char*, std::size_t), const char* a, int k) {
+    char buf[4096];
+    int rc = fn(a, k, buf, sizeof buf);
+    if (rc != B2G16_OK) throw error(rc, "cache path does not fit");
+    return buf;
+}
+inline std::string parameter_cache_identifier(const std::string& cache_prefix, const std::string& parameter_set_identifier) {
+    char buf[512];
+    int rc = b2g16_cache_identifier(cache_prefix.c_str(), parameter_set_identifier.c_str(), buf, sizeof buf);
+    if (rc != B2G16_OK) throw error(rc, "cache identifier does not fit");
+    return buf;
+}
+inline std::string parameter_cache_params_path(const std::string& id) { return cache_string(b2g16_cache_path, id.c_str(), 0); }
+inline std::string parameter_cache_verifying_key_path(const std::string& id) { return cache_string(b2g16_cache_path, id.c_str(), 1); }
+inline std::string parameter_cache_metadata_path(const std::string& id) { return cache_string(b2g16_cache_path, id.c_str(), 2); }
+struct cache_entry_metadata { std::uint64_t sector_size; };
+inline cache_entry_metadata read_cached_metadata(const std::string& path) {
+    cache_entry_metadata m{};
+    int rc = b2g16_meta_read(path.c_str(), &m.sector_size);
+    if (rc != B2G16_OK) throw error(rc, "cannot read " + path);
+    return m;
+}
+inline cache_entry_metadata write_cached_metadata(const std::string& path, cache_entry_metadata m) {
+    int rc = b2g16_meta_write(path.c_str(), m.sector_size);
+    if (rc != B2G16_OK) throw error(rc, "cannot write " + path);
+    return m;
+}
+
 }  // namespace b2g16
 
 namespace algebra {
@@ -210,6 +241,35 @@ template <class CurveType> struct r1cs_gg_ppzksnark {
     };
     struct verification_key_type {
         g1_value alpha_g1; g2_value beta_g2, gamma_g2, delta_g2; std::vector<g1_value> gamma_ABC_g1;
+        g1_value beta_g1, delta_g1;      // carried by the file formats only (the verifier does not use them)
+        // write_cached_verifying_key / read_cached_verifying_key (parameter_cache.hpp:131-145): the `.vk` cache entry
+        void write(const std::string& path) const {
+            b2g16_params p;
+            std::memset(&p, 0, sizeof p);
+            std::memcpy(p.alpha_g1, alpha_g1.data.data(), 96); std::memcpy(p.beta_g1, beta_g1.data.data(), 96);
+            std::memcpy(p.beta_g2, beta_g2.data.data(), 192); std::memcpy(p.gamma_g2, gamma_g2.data.data(), 192);
+            std::memcpy(p.delta_g1, delta_g1.data.data(), 96); std::memcpy(p.delta_g2, delta_g2.data.data(), 192);
+            p.n_ic = gamma_ABC_g1.size();
+            p.ic = const_cast<std::uint8_t*>(reinterpret_cast<const std::uint8_t*>(gamma_ABC_g1.data()));
+            int rc = b2g16_vk_file_write(path.c_str(), &p);
+            if (rc != B2G16_OK) throw b2g16::error(rc, "cannot write " + path);
+        }
+        static verification_key_type read(const std::string& path) {
+            b2g16_params* p = nullptr;
+            int rc = b2g16_vk_file_read(path.c_str(), &p);
+            if (rc != B2G16_OK) throw b2g16::error(rc, "cannot read " + path);
+            struct guard { b2g16_params* p; ~guard() { b2g16_params_free(p); } } g{p};
+            verification_key_type vk;
+            vk.from_params(*p);
+            return vk;
+        }
+        void from_params(const b2g16_params& p) {
+            std::memcpy(alpha_g1.data.data(), p.alpha_g1, 96); std::memcpy(beta_g1.data.data(), p.beta_g1, 96);
+            std::memcpy(beta_g2.data.data(), p.beta_g2, 192); std::memcpy(gamma_g2.data.data(), p.gamma_g2, 192);
+            std::memcpy(delta_g1.data.data(), p.delta_g1, 96); std::memcpy(delta_g2.data.data(), p.delta_g2, 192);
+            gamma_ABC_g1.resize(p.n_ic);
+            if (p.n_ic) std::memcpy(gamma_ABC_g1.data(), p.ic, 96 * p.n_ic);
+        }
     };
     typedef verification_key_type verifying_key_type;            // both spellings occur (scheme_params.hpp:44, multi_proof.hpp:43)
     // the `pvk` kept next to the mapped proving key (mapped_scheme_params.hpp:61): alpha/beta Miller value
@@ -332,12 +392,7 @@ template <class CurveType> struct r1cs_gg_ppzksnark {
             v.l = p->l; v.h = p->h; v.cs = &rv;
             b2g16_pk* pk = nullptr;
             c.check(b2g16_pk_load(c.get(), &v, &pk));
-            if (vk_out) {
-                std::memcpy(vk_out->alpha_g1.data.data(), p->alpha_g1, 96); std::memcpy(vk_out->beta_g2.data.data(), p->beta_g2, 192);
-                std::memcpy(vk_out->gamma_g2.data.data(), p->gamma_g2, 192); std::memcpy(vk_out->delta_g2.data.data(), p->delta_g2, 192);
-                vk_out->gamma_ABC_g1.resize(p->n_ic);
-                std::memcpy(vk_out->gamma_ABC_g1.data(), p->ic, 96 * p->n_ic);
-            }
+            if (vk_out) vk_out->from_params(*p);
             return proving_key_type(pk, nv);
         }
     };
@@ -362,6 +417,8 @@ typename Scheme::keypair_type generate(const typename Scheme::constraint_system_
     std::memcpy(kp.second.delta_g2.data.data(), vk.data() + 480, 192);
     kp.second.gamma_ABC_g1.resize(cs.n_in + 1);
     std::memcpy(kp.second.gamma_ABC_g1.data(), vk.data() + 672, 96 * (cs.n_in + 1));
+    c.check(b2g16_pk_export(c.get(), pk, 6, kp.second.beta_g1.data.data(), 96));     // for the .vk / .params files
+    c.check(b2g16_pk_export(c.get(), pk, 7, kp.second.delta_g1.data.data(), 96));
     return kp;
 }
 
