@@ -37,8 +37,10 @@ int b2g16_init(int device, void* stream, b2g16_ctx** out) {
         if (const char* e = getenv("B2G16_MSM_C")) c->msm_window_override = atoi(e);
         if (const char* e = getenv("B2G16_ACC_VARIANT")) c->acc_variant = atoi(e);
         if (const char* e = getenv("B2G16_SERIAL_LOG")) c->serial_above_log = atoi(e);
+        if (const char* e = getenv("B2G16_RED_BITS")) c->red_bits = atoi(e) != 0;
         if (const char* e = getenv("B2G16_TREE_LEVELS")) c->tree_levels = atoi(e);
         if (const char* e = getenv("B2G16_TREE_K")) { int v = atoi(e); if (v >= 2 && v <= 64) c->tree_k = v; }
+        if (const char* e = getenv("B2G16_TREE_K2")) { int v = atoi(e); if (v >= 2 && v <= 64) c->tree_k2 = v; }
         if (const char* e = getenv("B2G16_TREE_WGROUP")) c->tree_wgroup = atoi(e);
         if (const char* e = getenv("B2G16_RED_LOG")) { int v = atoi(e); if (v >= 1 && v <= 6) c->red_log = v; }
         ntt_init_roots(c);
@@ -394,8 +396,10 @@ int b2g16_set_tuning(b2g16_ctx* h, const char* key, int value) {
     if (k == "serial_above_log") c->serial_above_log = value;
     else if (k == "red_log" && value >= 1 && value <= 6) c->red_log = value;
     else if (k == "acc_variant") c->acc_variant = value;
+    else if (k == "red_bits") c->red_bits = value != 0;
     else if (k == "tree_levels") c->tree_levels = value;
     else if (k == "tree_k" && value >= 2 && value <= 64) c->tree_k = value;
+    else if (k == "tree_k2" && value >= 2 && value <= 64) c->tree_k2 = value;
     else if (k == "tree_wgroup") c->tree_wgroup = value;
     else if (k == "kernel_log") {
         c->klog_on = value != 0;

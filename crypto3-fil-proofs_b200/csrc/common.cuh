@@ -33,8 +33,10 @@ struct Ctx {
     int serial_above_log = 24;          // proofs with a larger domain run their five multiexps one after the other (B2G16_SERIAL_LOG)
     int red_log = 3;                    // log2 of the items per thread and level in the bucket reduction (B2G16_RED_LOG)
     int acc_variant = 102;              // bucket-accumulation kernel variant (B2G16_ACC_VARIANT)
+    int red_bits = 1;                   // finish the bucket reduction by bit decomposition once <= 16384 items per window are left (B2G16_RED_BITS)
     int tree_levels = -1;               // batched-affine tree levels before the XYZZ accumulate: -1 = by bucket occupancy, 0 = off (B2G16_TREE_LEVELS)
     int tree_k = 16;                    // outputs per thread in a tree level (B2G16_TREE_K)
+    int tree_k2 = 32;                   // values per thread in the upper levels of a tree level's product tree (B2G16_TREE_K2)
     int tree_wgroup = 0;                // windows per tree pass; 0 = as many as fit the free memory (B2G16_TREE_WGROUP)
     void* fixed_base[2] = {nullptr, nullptr};   // generator tables (G1, G2), built on first use
     cudaEvent_t ev_stage[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // prover stage marks (created once, b2g16_init)

@@ -415,13 +415,21 @@ struct Fq2 {
     }
 };
 
+}  // namespace b2
+
+#include "fp_wide.cuh"      // double-width products, separate reduction, lazy-reduction Fq2 product (needs Fq, Fq2 above)
+
+namespace b2 {
+
+// The Fq2 product everybody uses: three double-width products, two reductions (fp_wide.cuh) -- 744 multiplier slots
+// instead of the 900 of three full Montgomery products; measured 1.17e10 against 0.97e10 products/s on B200.
 #if defined(__CUDA_ARCH__)
-static __device__ __noinline__ void fq2_mul_call(Fq2* r, const Fq2* a, const Fq2* b) { *r = a->mul_inline(*b); }
+static __device__ __noinline__ void fq2_mul_call(Fq2* r, const Fq2* a, const Fq2* b) { *r = wide::fq2_mul_lazy<false>(*a, *b); }
 static __device__ __noinline__ void fq2_sqr_call(Fq2* r, const Fq2* a) { *r = a->sqr_inline(); }
 B2_HD Fq2 Fq2::operator*(const Fq2& o) const { Fq2 r; fq2_mul_call(&r, this, &o); return r; }
 B2_HD Fq2 Fq2::sqr() const { Fq2 r; fq2_sqr_call(&r, this); return r; }
 #else
-B2_HD Fq2 Fq2::operator*(const Fq2& o) const { return mul_inline(o); }
+B2_HD Fq2 Fq2::operator*(const Fq2& o) const { return wide::fq2_mul_lazy<false>(*this, o); }
 B2_HD Fq2 Fq2::sqr() const { return sqr_inline(); }
 #endif
 

@@ -20,6 +20,9 @@
 #pragma once
 #include "common.cuh"
 #include <cstdlib>
+#include <cstdio>
+#include <utility>
+#include <vector>
 #include "msm_digits.cuh"
 #include "msm_tree.cuh"
 
@@ -205,6 +208,7 @@ msm_accumulate_kernel(const Affine<F>* __restrict__ bases, const uint32_t* __res
 // boundaries leaves one "tail" piece (its first part, at the end of a chunk) and "head" pieces (its
 // continuations, at the start of later chunks) that msm_fix_pieces_kernel folds afterwards.
 constexpr uint32_t NO_BUCKET = 0xffffffffu;
+constexpr uint32_t RED_BITS_MAX = 16384;      // items per window at which the bucket reduction switches to the bit-decomposition tail
 
 // DIRECT: the entries are the points themselves (bases[e], the output of the affine tree levels, identities possible)
 // instead of (index, sign) references into the key.
@@ -379,6 +383,56 @@ msm_reduce_level_kernel(const Xyzz<F>* __restrict__ a_in, const Xyzz<F>* __restr
     xyzz_add_call(&asum, &acc);
     a_out[(size_t)w * T + t] = asum;
     r_out[(size_t)w * T + t] = run;
+}
+
+// ---- 5''. tail of the bucket reduction by bit decomposition ---------------------------------
+// V = sum_t a_t + 2^log_s sum_t t r_t over `count` items per window.  sum_t t r_t = sum_b 2^b S_b with
+// S_b = sum of the r_t whose index has bit b set: NB independent plain sums (plus one over the a_t), each a
+// CTA-wide tree -- ~16 dependent group operations -- where every further level of the recursion above is a
+// chain of ~30 on a handful of threads.  The work doubles (NB / 2 + 1 additions per item instead of 3), which
+// is why the big first level(s) stay with the running-sum form.
+// grid (NB + 1, W); block 256.  CTA (b, w): b < NB -> S_b of window w, b == NB -> sum of the a_t.
+template <class F> __global__ void __launch_bounds__(256)
+msm_reduce_bits_kernel(const Xyzz<F>* __restrict__ a_in, const Xyzz<F>* __restrict__ r_in, uint32_t count, uint32_t stride, int NB, Xyzz<F>* __restrict__ sums) {
+    __shared__ Xyzz<F> warp_part[8];
+    const int b = blockIdx.x, w = blockIdx.y;
+    const Xyzz<F>* src = (b == NB ? a_in : r_in) + (size_t)w * stride;
+    Xyzz<F> acc = Xyzz<F>::identity();
+    if (b == NB) {
+        for (uint32_t t = threadIdx.x; t < count; t += blockDim.x) { Xyzz<F> v = src[t]; xyzz_add_call(&acc, &v); }
+    } else {
+        // j-th index with bit b set: the high part of j moves up by one position, bit b is forced on
+        const uint32_t low = (1u << b) - 1u;
+        for (uint32_t j = threadIdx.x;; j += blockDim.x) {
+            const uint32_t t = ((j >> b) << (b + 1)) | (1u << b) | (j & low);
+            if (t >= count) break;                       // t grows with j
+            Xyzz<F> v = src[t]; xyzz_add_call(&acc, &v);
+        }
+    }
+    for (int d = 16; d >= 1; d >>= 1) { Xyzz<F> o = xyzz_shfl_down(acc, d); xyzz_add_call(&acc, &o); }
+    const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+    if (lane == 0) warp_part[wid] = acc;
+    __syncthreads();
+    if (wid == 0) {
+        acc = lane < 8 ? warp_part[lane] : Xyzz<F>::identity();
+        for (int d = 4; d >= 1; d >>= 1) { Xyzz<F> o = xyzz_shfl_down(acc, d); xyzz_add_call(&acc, &o); }
+        if (lane == 0) sums[(size_t)w * (NB + 1) + b] = acc;
+    }
+}
+// one warp per window: lane b doubles S_b b times (all lanes at once), a shuffle tree adds them, then the 2^log_s
+// factor and the sum of the a_t
+template <class F> __global__ void __launch_bounds__(32)
+msm_reduce_bits_final_kernel(const Xyzz<F>* __restrict__ sums, int NB, int log_s, Xyzz<F>* __restrict__ win) {
+    const int w = blockIdx.x, lane = threadIdx.x;
+    Xyzz<F> acc = lane < NB ? sums[(size_t)w * (NB + 1) + lane] : Xyzz<F>::identity();
+    for (int k = 0; k < NB; ++k) if (k < lane) xyzz_dbl_call(&acc);
+    for (int d = 16; d >= 1; d >>= 1) { Xyzz<F> o = xyzz_shfl_down(acc, d); xyzz_add_call(&acc, &o); }
+    if (lane == 0) {
+        for (int k = 0; k < log_s; ++k) xyzz_dbl_call(&acc);
+        Xyzz<F> a = sums[(size_t)w * (NB + 1) + NB];
+        xyzz_add_call(&acc, &a);
+        win[w] = acc;
+    }
 }
 
 // ---- 6. Horner over windows + affine output --------------------------------------------
@@ -585,6 +639,14 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
     const bool timed = ctx->time_msm;
     if (timed) for (auto& e : ev) B2_CUDA(cudaEventCreate(&e));
     auto mark = [&](int i) { if (timed) B2_CUDA(cudaEventRecord(ev[i], st)); };
+    // B2G16_MSM_TRACE=1 (with timing on): a CUDA event after every step of the accumulation / reduction, printed to
+    // stderr once the multiexp is done -- the step-by-step split that ncu's serialised per-launch times cannot give
+    static const bool trace_on = getenv("B2G16_MSM_TRACE") != nullptr;
+    std::vector<std::pair<const char*, cudaEvent_t>> tr;
+    auto tmark = [&](const char* label) {
+        if (!(timed && trace_on)) return;
+        cudaEvent_t e; B2_CUDA(cudaEventCreate(&e)); B2_CUDA(cudaEventRecord(e, st)); tr.push_back({label, e});
+    };
 
     mark(0);
     B2_CUDA(cudaMemsetAsync(hist.get(), 0, (nb + 1) * sizeof(uint32_t), st));
@@ -608,7 +670,7 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
         if (kl.e0) B2_CUDA(cudaEventRecord(kl.e0, st));
         if (tree_levels > 0) {
             // ---- affine tree levels, then the XYZZ accumulate over what is left; windows in groups that fit the memory
-            const uint32_t K = ctx->tree_k, K2 = 32;
+            const uint32_t K = ctx->tree_k, K2 = ctx->tree_k2;
             auto caps = [&](size_t entries, uint32_t nbg, size_t* cap /*levels*/) {
                 size_t e = entries;
                 for (int l = 0; l < tree_levels; ++l) { e = (e + nbg) / 2 + 1; cap[l] = e; }
@@ -647,31 +709,40 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
                 const uint32_t nbg = (uint32_t)(w1 - w0) * B, b0 = (uint32_t)w0 * B;
                 caps(n * (size_t)(w1 - w0), nbg, cap);
                 TreeIn<F> in{d_bases, sorted.get(), nullptr, off.get() + b0};
+                tmark("begin");
                 for (int l = 0; l < tree_levels; ++l) {
                     uint32_t* off_o = (l & 1) ? offB.get() : offA.get();
                     Affine<F>* pts_o = (l & 1) ? ptsB.get() : ptsA.get();
                     scan_u32(ctx, st, in.off, off_o, nbg, 2, 2, tile_sums.get());
                     const uint32_t* e_out = off_o + nbg;
                     const uint32_t t1 = tree_count_at((uint32_t)cap[l], 1, K, K2);
+                    tmark("scan");
                     tree_up0_kernel<F><<<(t1 + 127) / 128, 128, 0, st>>>(in, off_o, nbg, K, pp0.get(), val[1].get());
+                    tmark("up0");
                     int dt = 1;
                     while (tree_count_at((uint32_t)cap[l], dt, K, K2) > TREE_TOP) {
                         const uint32_t tn = tree_count_at((uint32_t)cap[l], dt + 1, K, K2);
                         tree_up_kernel<F><<<(tn + 127) / 128, 128, 0, st>>>(val[dt].get(), e_out, dt, K, K2, ppd[dt].get(), val[dt + 1].get());
                         ++dt;
                     }
+                    tmark("up");
                     tree_top_kernel<F><<<1, 32, 0, st>>>(val[dt].get(), e_out, dt, K, K2, top_scratch.get());
+                    tmark("top");
                     for (int d = dt - 1; d >= 1; --d) {
                         const uint32_t tn = tree_count_at((uint32_t)cap[l], d + 1, K, K2);
                         tree_down_kernel<F><<<(tn + 127) / 128, 128, 0, st>>>(val[d].get(), e_out, d, K, K2, ppd[d].get(), val[d + 1].get());
                     }
+                    tmark("down");
                     tree_down0_kernel<F><<<(t1 + 127) / 128, 128, 0, st>>>(in, off_o, nbg, K, pp0.get(), val[1].get(), pts_o);
+                    tmark("down0");
                     ctx->launches += 3 + 2 * (dt - 1);
                     in = TreeIn<F>{nullptr, nullptr, pts_o, off_o};
                 }
                 if (sizeof(F) > 48) msm_accumulate_chunked_kernel<F, 64, 4, true><<<148 * 4, 64, 0, st>>>(in.pts, nullptr, in.off, nbg, seg_acc.get() + b0, head, tail, hb, tb);
                 else msm_accumulate_chunked_kernel<F, 128, 2, true><<<148 * 2, 128, 0, st>>>(in.pts, nullptr, in.off, nbg, seg_acc.get() + b0, head, tail, hb, tb);
+                tmark("xyzz_tail");
                 msm_fix_pieces_kernel<F><<<grid_for((size_t)n_chunks * 32, 128, 148 * 16), 128, 0, st>>>(seg_acc.get() + b0, head, tail, hb, tb, n_chunks);
+                tmark("fix_pieces");
                 ctx->launches += 2;
             }
             if (kl.e1) B2_CUDA(cudaEventRecord(kl.e1, st));
@@ -713,10 +784,25 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
         for (;;) {
             const uint32_t T = (count + RED_PER - 1) / RED_PER;
             msm_reduce_level_kernel<F><<<(W * T + 127) / 128, 128, 0, st>>>(a_in, r_in, count, stride, shift_one, RED_PER, log_s, red_a[side].get(), red_r[side].get(), T, W);
+            tmark("reduce_level");
             ctx->launches++;
             a_in = red_a[side].get(); r_in = red_r[side].get();
             if (T == 1) break;
             count = T; stride = T; log_s += red_log; shift_one = 0; side ^= 1;
+            if (ctx->red_bits && count <= RED_BITS_MAX) {
+                // few enough items left: finish by bit decomposition (two short launches instead of 3-5 latency-bound levels)
+                int NB = 0;
+                while ((1u << NB) < count) ++NB;                        // indices 0 .. count-1 fit NB bits
+                Xyzz<F>* sums = red_a[side].get();                      // W * (NB + 1) <= W * T1 slots
+                Xyzz<F>* out = red_r[side].get();
+                msm_reduce_bits_kernel<F><<<dim3(NB + 1, W), 256, 0, st>>>(a_in, r_in, count, stride, NB, sums);
+                tmark("reduce_bits");
+                msm_reduce_bits_final_kernel<F><<<W, 32, 0, st>>>(sums, NB, log_s, out);
+                tmark("reduce_bits_final");
+                ctx->launches += 2;
+                a_in = out;
+                break;
+            }
         }
         win = a_in;
     } else {
@@ -739,6 +825,11 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
         B2_CUDA(cudaEventSynchronize(ev[5]));
         for (int i = 0; i < 5; ++i) B2_CUDA(cudaEventElapsedTime(&ctx->msm_ms[i], ev[i], ev[i + 1]));
         for (auto& e : ev) cudaEventDestroy(e);
+        for (size_t i = 1; i < tr.size(); ++i) {
+            float ms = 0.f; cudaEventElapsedTime(&ms, tr[i - 1].second, tr[i].second);
+            fprintf(stderr, "msm_trace g%d c=%d %s %.3f ms\n", sizeof(F) > 48 ? 2 : 1, c, tr[i].first, ms);
+        }
+        for (auto& t : tr) cudaEventDestroy(t.second);
     }
 }
 

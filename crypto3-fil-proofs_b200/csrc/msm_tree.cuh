@@ -82,6 +82,11 @@ template <class F> B2_HD Affine<F> tree_entry(const TreeIn<F>& in, uint32_t e) {
     }
     return tree_ld_affine(in.pts + e);
 }
+// x coordinate of entry e alone (the sign bit of a level-0 reference does not touch x)
+template <class F> B2_HD F tree_entry_x(const TreeIn<F>& in, uint32_t e) {
+    if (in.sorted) return tree_ld_field(&in.bases[in.sorted[e] & 0x7fffffffu].x);
+    return tree_ld_field(&in.pts[e].x);
+}
 
 // What one output of a level is.  KIND_ADD / KIND_DBL need the inverse of `d`.
 enum { TREE_COPY0 = 0, TREE_COPY1 = 1, TREE_ADD = 2, TREE_DBL = 3, TREE_ZERO = 4 };
@@ -123,9 +128,16 @@ template <class F> B2_HD void tree_up0_body(const TreeIn<F>& in, const uint32_t*
         const bool has_pair = i0 + 1 < in.off[b + 1];
         tree_st_field(pp + o, prod);
         if (!has_pair) continue;
-        const Affine<F> p0 = tree_entry(in, i0), p1 = tree_entry(in, i0 + 1);
+        // The denominator of an ordinary addition needs the two x coordinates only (half the bytes of the gather):
+        // x != 0 rules out the identity, x0 != x1 the doubling / cancellation cases; everything else takes the full path.
         F d;
-        const int kind = tree_classify(p0, p1, true, d);
+        int kind;
+        const F x0 = tree_entry_x(in, i0), x1 = tree_entry_x(in, i0 + 1);
+        if (!x0.is_zero() && !x1.is_zero() && x0 != x1) { d = x1 - x0; kind = TREE_ADD; }
+        else {
+            const Affine<F> p0 = tree_entry(in, i0), p1 = tree_entry(in, i0 + 1);
+            kind = tree_classify(p0, p1, true, d);
+        }
         if (kind == TREE_ADD || kind == TREE_DBL) { prod = any ? prod * d : d; any = true; }
     }
     tree_st_field(tot + t, prod);

@@ -47,6 +47,29 @@ int emu_fr_op(int op, const uint8_t* a, const uint8_t* b, size_t n, uint8_t* out
 int emu_fq_op(int op, const uint8_t* a, const uint8_t* b, size_t n, uint8_t* out) { return field_op<Fq>(op, a, b, n, out); }
 int emu_g1_sum(int mode, const uint8_t* p, size_t n, uint8_t* out) { return sum_points<Fq, 96>(mode, p, n, out); }
 int emu_g2_sum(int mode, const uint8_t* p, size_t n, uint8_t* out) { return sum_points<Fq2, 192>(mode, p, n, out); }
+// fp_wide.cuh: which = 0 split product + reduction, 1 Karatsuba product + reduction (Fq, 48-byte canonical operands);
+// which = 2 / 3: Fq2 product with lazy reduction, schoolbook / Karatsuba (96-byte operands c0 || c1).  -1 on a non-canonical operand.
+int emu_wide_mul(int which, const uint8_t* a, const uint8_t* b, size_t n, uint8_t* out) {
+    const int comps = which >= 2 ? 2 : 1;
+    for (size_t i = 0; i < n; ++i) {
+        Fq x[2], y[2];
+        for (int k = 0; k < comps; ++k) {
+            uint32_t ca[12], cb[12];
+            memcpy(ca, a + (i * comps + k) * 48, 48); memcpy(cb, b + (i * comps + k) * 48, 48);
+            if (Fq::geq_p(ca) || Fq::geq_p(cb)) return -1;
+            x[k] = Fq::from_canonical(ca); y[k] = Fq::from_canonical(cb);
+        }
+        Fq r[2];
+        if (which == 0) r[0] = wide::fq_mul<false>(x[0], y[0]);
+        else if (which == 1) r[0] = wide::fq_mul<true>(x[0], y[0]);
+        else {
+            const Fq2 z = which == 2 ? wide::fq2_mul_lazy<false>(Fq2{x[0], x[1]}, Fq2{y[0], y[1]}) : wide::fq2_mul_lazy<true>(Fq2{x[0], x[1]}, Fq2{y[0], y[1]});
+            r[0] = z.c0; r[1] = z.c1;
+        }
+        for (int k = 0; k < comps; ++k) { uint32_t c[12]; r[k].to_canonical(c); memcpy(out + (i * comps + k) * 48, c, 48); }
+    }
+    return 0;
+}
 }
 
 // ---------------------------------------------------------------------------------------

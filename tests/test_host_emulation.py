@@ -93,6 +93,41 @@ def test_field_random_vs_oracle(emu, oracle, field, size):
     assert np.array_equal(_op(emu, field, "sqr", a), oracle.field_op(field, "sqr", a))
 
 
+def test_wide_products_vs_oracle(emu, oracle):
+    """fp_wide.cuh: the split product + separate Montgomery reduction, its Karatsuba form and the lazy-reduction Fq2
+    product (the one Fq2::operator* uses) against big-integer arithmetic."""
+    rng = np.random.Generator(np.random.PCG64(31))
+    n = 6000
+    P = 0x1a0111ea397fe69a4b1ba7b6434bacd764774b84f38512bf6730d2a0f6b0f6241eabfffeb153ffffb9feffffffffaaab
+    a = rng.integers(0, 256, size=(2 * n, 48), dtype=np.uint8); a[:, 47] &= 0x0F
+    b = rng.integers(0, 256, size=(2 * n, 48), dtype=np.uint8); b[:, 47] &= 0x0F
+    edge = [0, 1, P - 1, P - 2, (1 << 192) - 1, ((1 << 380) - 1) & ~((1 << 192) - 1), (1 << 192), P >> 1]
+    for i, v in enumerate(edge):
+        a[i] = np.frombuffer(v.to_bytes(48, "little"), dtype=np.uint8)
+        b[len(edge) - 1 - i] = np.frombuffer(v.to_bytes(48, "little"), dtype=np.uint8)
+        a[2 * i + 20] = a[i]; b[2 * i + 21] = b[i]
+    ai = [int.from_bytes(r.tobytes(), "little") for r in a]
+    bi = [int.from_bytes(r.tobytes(), "little") for r in b]
+
+    def enc(vals):
+        return np.frombuffer(b"".join(v.to_bytes(48, "little") for v in vals), dtype=np.uint8).reshape(-1, 48)
+
+    want = enc([x * y % P for x, y in zip(ai, bi)])
+    for which in (0, 1):
+        out = np.zeros_like(a)
+        assert emu.emu_wide_mul(which, _p(a), _p(b), C.c_size_t(2 * n), _p(out)) == 0
+        assert np.array_equal(out, want), which
+    w2 = []
+    for k in range(n):
+        a0, a1, b0, b1 = ai[2 * k], ai[2 * k + 1], bi[2 * k], bi[2 * k + 1]
+        w2 += [(a0 * b0 - a1 * b1) % P, (a0 * b1 + a1 * b0) % P]
+    want2 = enc(w2)
+    for which in (2, 3):
+        out = np.zeros_like(a)
+        assert emu.emu_wide_mul(which, _p(a), _p(b), C.c_size_t(n), _p(out)) == 0
+        assert np.array_equal(out, want2), which
+
+
 def test_curve_ops_vs_oracle(emu, oracle):
     rng = np.random.Generator(np.random.PCG64(77))
     k = codec.random_fr(40, rng)
