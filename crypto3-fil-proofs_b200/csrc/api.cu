@@ -401,6 +401,7 @@ int b2g16_set_tuning(b2g16_ctx* h, const char* key, int value) {
     else if (k == "tree_k" && value >= 2 && value <= 64) c->tree_k = value;
     else if (k == "tree_k2" && value >= 2 && value <= 64) c->tree_k2 = value;
     else if (k == "tree_wgroup") c->tree_wgroup = value;
+    else if (k == "key_chunk_mib" && value >= 1 && value <= 1024) c->key_chunk_mib = value;
     else if (k == "kernel_log") {
         c->klog_on = value != 0;
         cudaSetDevice(c->device);

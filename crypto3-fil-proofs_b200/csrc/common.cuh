@@ -37,6 +37,7 @@ struct Ctx {
     int tree_levels = -1;               // batched-affine tree levels before the XYZZ accumulate: -1 = by bucket occupancy, 0 = off (B2G16_TREE_LEVELS)
     int tree_k = 16;                    // outputs per thread in a tree level (B2G16_TREE_K)
     int tree_k2 = 32;                   // values per thread in the upper levels of a tree level's product tree (B2G16_TREE_K2)
+    int key_chunk_mib = 32;             // pinned ring slot of the streamed parameter-file loader, MiB ("key_chunk_mib")
     int tree_wgroup = 0;                // windows per tree pass; 0 = as many as fit the free memory (B2G16_TREE_WGROUP)
     void* fixed_base[2] = {nullptr, nullptr};   // generator tables (G1, G2), built on first use
     cudaEvent_t ev_stage[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};   // prover stage marks (created once, b2g16_init)

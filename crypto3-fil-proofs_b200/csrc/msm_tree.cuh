@@ -216,11 +216,18 @@ template <class F> B2_HD void tree_down0_body(const TreeIn<F>& in, const uint32_
 #if defined(__CUDACC__)
 // ---- kernels: one thread per body call.  Grids are sized from host-side upper bounds of the entry counts (the true
 // count is device data: off_out[n_buckets]); surplus threads return at once.
-template <class F> __global__ void __launch_bounds__(128) tree_up0_kernel(TreeIn<F> in, const uint32_t* __restrict__ off_out, uint32_t n_buckets, uint32_t K,
+// CTAs per SM the big level kernels are compiled for.  The G2 forms sit at the 255-register cap (two warps per scheduler,
+// 58 % of the multiplier rate in tree_down0); forcing 3 or 4 CTAs per SM (-DB2_TREE_G2_MINB=3 / 4: 168 / 128 registers,
+// the rest spilled) was measured slower: 64.7 / 66.4 ms against 54.4 ms for the five down0 launches of a 2^22 multiexp.
+#ifndef B2_TREE_G2_MINB
+#define B2_TREE_G2_MINB 1
+#endif
+template <class F> struct TreeMinBlocks { static constexpr int value = sizeof(F) > 48 ? B2_TREE_G2_MINB : 1; };
+template <class F> __global__ void __launch_bounds__(128, TreeMinBlocks<F>::value) tree_up0_kernel(TreeIn<F> in, const uint32_t* __restrict__ off_out, uint32_t n_buckets, uint32_t K,
                                                                           F* __restrict__ pp, F* __restrict__ tot) {
     tree_up0_body<F>(in, off_out, n_buckets, K, blockIdx.x * blockDim.x + threadIdx.x, pp, tot);
 }
-template <class F> __global__ void __launch_bounds__(128) tree_down0_kernel(TreeIn<F> in, const uint32_t* __restrict__ off_out, uint32_t n_buckets, uint32_t K,
+template <class F> __global__ void __launch_bounds__(128, TreeMinBlocks<F>::value) tree_down0_kernel(TreeIn<F> in, const uint32_t* __restrict__ off_out, uint32_t n_buckets, uint32_t K,
                                                                             const F* __restrict__ pp, const F* __restrict__ inv_tot, Affine<F>* __restrict__ out) {
     tree_down0_body<F>(in, off_out, n_buckets, K, blockIdx.x * blockDim.x + threadIdx.x, pp, inv_tot, out);
 }

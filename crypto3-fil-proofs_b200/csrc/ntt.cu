@@ -62,7 +62,11 @@ void ntt_init_roots(Ctx* c) {
     Fr w = host_root_of_unity(NTT_ROOT_LOG);
     c->roots_fwd = make_table(c, w, Fr::one(), 0, 1u << (NTT_ROOT_LOG - 1));
     c->roots_inv = make_table(c, w.inv(), Fr::one(), 0, 1u << (NTT_ROOT_LOG - 1));
-    B2_CUDA(cudaFuncSetAttribute(ntt_pass_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, 2 * sizeof(uint4) << NTT_TILE_LOG));
+    const int smem = (int)(2 * sizeof(uint4) << NTT_TILE_LOG);
+    B2_CUDA(cudaFuncSetAttribute(ntt_pass_kernel<256, 3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    B2_CUDA(cudaFuncSetAttribute(ntt_pass_kernel<128, 3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    B2_CUDA(cudaFuncSetAttribute(ntt_pass_kernel<256, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    B2_CUDA(cudaFuncSetAttribute(ntt_pass_kernel<256, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
 }
 
 NttDomain* ntt_domain(Ctx* c, int log_n) {
@@ -138,8 +142,17 @@ static void launch_pass(Ctx* c, const Fr* src, Fr* dst, const NttPass& p) {
     const size_t smem = 2 * sizeof(uint4) * (size_t)T;
     const int max_grid = 148 * 3 * 4;                      // 3 resident CTAs per SM, a few waves
     int grid = (int)(tiles < (uint64_t)max_grid ? tiles : (uint64_t)max_grid);
-    int block = T / 2 < 256 ? (T / 2 < 32 ? 32 : T / 2) : 256;
-    ntt_pass_kernel<<<grid, block, smem, c->stream>>>(src, dst, p);
+    static const int variant = getenv("B2G16_NTT_VARIANT") ? atoi(getenv("B2G16_NTT_VARIANT")) : 0;
+    if (variant == 0) {
+        const int block = T / 2 < 256 ? (T / 2 < 32 ? 32 : T / 2) : 256;
+        ntt_pass_kernel<256, 3, false><<<grid, block, smem, c->stream>>>(src, dst, p);
+    } else {
+        const int cap = variant == 1 ? 128 : 256;
+        const int block = T / 8 < cap ? (T / 8 < 32 ? 32 : T / 8) : cap;     // one register-round slot = 8 elements
+        if (variant == 1) ntt_pass_kernel<128, 3, true><<<grid, block, smem, c->stream>>>(src, dst, p);
+        else if (variant == 2) ntt_pass_kernel<256, 2, true><<<grid, block, smem, c->stream>>>(src, dst, p);
+        else ntt_pass_kernel<256, 1, true><<<grid, block, smem, c->stream>>>(src, dst, p);
+    }
     c->launches++;
     B2_CUDA(cudaGetLastError());
 }

@@ -102,6 +102,12 @@ B2_HD uint32_t bitrev_u32(uint32_t x, int bits) {
     return r;
 }
 
+// Shared-memory slot of tile element e.  The register rounds below read a tile with lane strides of 8 or 32 elements
+// (the rows a thread owns are contiguous in the last round), which would put a quarter-warp's 16-byte accesses on the same
+// banks; XOR-ing the low three index bits with the next three spreads those strides over all 32 banks and only permutes
+// elements inside 128-byte blocks, so unit-stride accesses stay conflict-free.  Tiles smaller than 64 elements are left alone.
+B2_HD int ntt_swz(int e, int tile_log) { return tile_log >= 6 ? (e ^ ((e >> 3) & 7)) : e; }
+
 // ---- tile geometry -------------------------------------------------------------
 // tile element e in [0, 2^(k+logc)):  (row, col) and its global position.
 struct NttTile {
@@ -162,7 +168,7 @@ B2_HD void ntt_phase_load(const NttPass& p, const NttTile& t, const Fr* data, ui
     if (p.fuse_abc) x = (x * fr_load(p.src_b + g) - fr_load(p.src_c + g)) * p.zinv;
     if (p.scale_mode == 1) x = x * ntt_scale(p, g);
     if (p.tw_mode == 2 && row != 0) x = x * ntt_twiddle(p, t.col0 + col, (uint32_t)row);
-    const int dst = p.dit ? t.elem((int)bitrev_u32((uint32_t)row, p.k), col) : e;
+    const int dst = ntt_swz(p.dit ? t.elem((int)bitrev_u32((uint32_t)row, p.k), col) : e, p.k + p.logc);
     fr_to_planes(x, s_lo[dst], s_hi[dst]);
 }
 // Twiddle of the butterfly (row j of the half-block, column col) in the stage with half-size h = 2^hs.
@@ -195,7 +201,7 @@ B2_HD void ntt_phase_stage(const NttPass& p, const NttTile& t, uint4* s_lo, uint
     int h = 1 << hs;
     int j = rb & (h - 1), grp = rb >> hs;
     int r0 = (grp << (hs + 1)) | j;
-    int e0 = t.elem(r0, col), e1 = t.elem(r0 + h, col);
+    int e0 = ntt_swz(t.elem(r0, col), p.k + p.logc), e1 = ntt_swz(t.elem(r0 + h, col), p.k + p.logc);
     Fr u = fr_from_planes(s_lo[e0], s_hi[e0]);
     Fr v = fr_from_planes(s_lo[e1], s_hi[e1]);
     Fr w; bool neg;
@@ -212,11 +218,89 @@ B2_HD void ntt_phase_stage(const NttPass& p, const NttTile& t, uint4* s_lo, uint
     fr_to_planes(s, s_lo[e0], s_hi[e0]);
     fr_to_planes(d, s_lo[e1], s_hi[e1]);
 }
+// One butterfly on two values held in registers (same arithmetic as ntt_phase_stage), twiddle already fetched
+B2_HD void ntt_butterfly(bool dit, bool has_w, bool neg, const Fr& w, Fr& u, Fr& v) {
+    if (dit) {
+        if (has_w) v = v * w;
+        const Fr s = neg ? u - v : u + v, d = neg ? u + v : u - v;
+        u = s; v = d;
+    } else {
+        const Fr s = u + v;
+        Fr d = neg ? v - u : u - v;
+        if (has_w) d = d * w;
+        u = s; v = d;
+    }
+}
+// R consecutive stages (half-sizes 2^hmin .. 2^(hmin+R-1)) of the tile's row transform on the 2^R elements one thread
+// keeps in registers: rows base | (m << hmin), m < 2^R, one column.  A tile has 2^(k+logc-R) such slots; consecutive
+// slots are adjacent in shared memory.  One shared-memory round trip and one barrier per R stages instead of per stage,
+// and the index arithmetic is paid once per 2^R elements.
+template <int R, bool DIT> B2_HD void ntt_phase_round(const NttPass& p, const NttTile& t, uint4* s_lo, uint4* s_hi, int hmin, int slot) {
+    constexpr int M = 1 << R;
+    const int hmax = hmin + R - 1, tile_log = p.k + p.logc;
+    int col, low, high;
+    if (t.contiguous) {
+        low = slot & ((1 << hmin) - 1);
+        const int q = slot >> hmin, nh = p.k - 1 - hmax;
+        high = q & ((1 << nh) - 1); col = q >> nh;
+    } else {
+        col = slot & ((1 << p.logc) - 1);
+        const int q = slot >> p.logc;
+        low = q & ((1 << hmin) - 1); high = q >> hmin;
+    }
+    const int base = (high << (hmax + 1)) | low;
+    Fr v[M];
+#pragma unroll
+    for (int m = 0; m < M; ++m) { const int e = ntt_swz(t.elem(base | (m << hmin), col), tile_log); v[m] = fr_from_planes(s_lo[e], s_hi[e]); }
+    // all 2^R - 1 twiddles of the round first (the stage with half-size bit b has 2^b distinct ones: the row's bits below
+    // b), so that their global-memory latencies overlap instead of queueing in front of each stage
+    Fr w[M - 1 > 0 ? M - 1 : 1];
+    uint32_t has_mask = 0, neg_mask = 0;
+#pragma unroll
+    for (int b = 0; b < R; ++b) {
+#pragma unroll
+        for (int ml = 0; ml < (1 << b); ++ml) {
+            const int idx = (1 << b) - 1 + ml, hs = hmin + b;
+            bool neg;
+            const bool has_w = ntt_stage_twiddle(p, t, hs, (base | (ml << hmin)) & ((1 << hs) - 1), col, w[idx], neg);
+            has_mask |= (has_w ? 1u : 0u) << idx; neg_mask |= (neg ? 1u : 0u) << idx;
+        }
+    }
+#pragma unroll
+    for (int s = 0; s < R; ++s) {
+        const int b = DIT ? s : R - 1 - s;            // DIF: largest half-size first; DIT: smallest first (compile-time: v[] stays in registers)
+#pragma unroll
+        for (int m = 0; m < M; ++m) {
+            if ((m >> b) & 1) continue;
+            const int idx = (1 << b) - 1 + (m & ((1 << b) - 1));
+            ntt_butterfly(DIT, (has_mask >> idx) & 1u, (neg_mask >> idx) & 1u, w[idx], v[m], v[m | (1 << b)]);
+        }
+    }
+#pragma unroll
+    for (int m = 0; m < M; ++m) { const int e = ntt_swz(t.elem(base | (m << hmin), col), tile_log); fr_to_planes(v[m], s_lo[e], s_hi[e]); }
+}
+// Rounds of a pass: the k stages in execution order, three at a time; the last round takes what is left.
+// Round r covers execution-order stages [3r, min(3r+3, k)): DIF -> half-size bits hmin = k - 3r - R, DIT -> hmin = 3r.
+B2_HD int ntt_round_count(const NttPass& p) { return (p.k + 2) / 3; }
+B2_HD int ntt_round_size(const NttPass& p, int r) { const int left = p.k - 3 * r; return left < 3 ? left : 3; }
+B2_HD int ntt_round_hmin(const NttPass& p, int r) { return p.dit ? 3 * r : p.k - 3 * r - ntt_round_size(p, r); }
+B2_HD void ntt_phase_round_any(const NttPass& p, const NttTile& t, uint4* s_lo, uint4* s_hi, int r, int slot) {
+    const int R = ntt_round_size(p, r), hmin = ntt_round_hmin(p, r);
+    if (p.dit) {
+        if (R == 3) ntt_phase_round<3, true>(p, t, s_lo, s_hi, hmin, slot);
+        else if (R == 2) ntt_phase_round<2, true>(p, t, s_lo, s_hi, hmin, slot);
+        else ntt_phase_round<1, true>(p, t, s_lo, s_hi, hmin, slot);
+    } else {
+        if (R == 3) ntt_phase_round<3, false>(p, t, s_lo, s_hi, hmin, slot);
+        else if (R == 2) ntt_phase_round<2, false>(p, t, s_lo, s_hi, hmin, slot);
+        else ntt_phase_round<1, false>(p, t, s_lo, s_hi, hmin, slot);
+    }
+}
 // stage order: DIF runs half-sizes k-1 .. 0, DIT 0 .. k-1
 B2_HD int ntt_stage_hs(const NttPass& p, int i) { return p.dit ? i : p.k - 1 - i; }
 B2_HD void ntt_phase_store(const NttPass& p, const NttTile& t, Fr* data, const uint4* s_lo, const uint4* s_hi, int e) {
     int row = t.row_of(e), col = t.col_of(e);          // output row k1 (natural order)
-    int src = p.dit ? e : t.elem((int)bitrev_u32((uint32_t)row, p.k), col);
+    int src = ntt_swz(p.dit ? e : t.elem((int)bitrev_u32((uint32_t)row, p.k), col), p.k + p.logc);
     Fr x = fr_from_planes(s_lo[src], s_hi[src]);
     uint64_t g = t.gpos(row, col);
     if (p.tw_mode == 1 && row != 0) x = x * ntt_twiddle(p, t.col0 + col, (uint32_t)row);
@@ -226,7 +310,11 @@ B2_HD void ntt_phase_store(const NttPass& p, const NttTile& t, Fr* data, const u
 }
 
 #if defined(__CUDACC__)
-static __global__ void __launch_bounds__(256) ntt_pass_kernel(const Fr* src, Fr* data, const NttPass p) {
+// THREADS x MINB: CTA size and CTAs per SM the kernel is compiled for; ROUNDS: three stages at a time on eight values in
+// registers (ntt_phase_round) instead of one stage per barrier (ntt_phase_stage).  A 2048-element tile is 64 KB of shared
+// memory, so at most three CTAs fit an SM.  B2G16_NTT_VARIANT: 0 = one stage per barrier, 256 x 3 (24 warps per SM);
+// 1 / 2 / 3 = register rounds at 128 x 3 (168 registers), 256 x 2 (128 registers, spills), 256 x 1 (no spills, 8 warps).
+template <int THREADS, int MINB, bool ROUNDS> static __global__ void __launch_bounds__(THREADS, MINB) ntt_pass_kernel(const Fr* src, Fr* data, const NttPass p) {
     extern __shared__ uint4 smem[];
     const int T = 1 << (p.k + p.logc);
     uint4* s_lo = smem;
@@ -235,10 +323,19 @@ static __global__ void __launch_bounds__(256) ntt_pass_kernel(const Fr* src, Fr*
         const NttTile t = ntt_make_tile(p, tile_id);
         for (int e = threadIdx.x; e < T; e += blockDim.x) ntt_phase_load(p, t, src, s_lo, s_hi, e);
         __syncthreads();
-        for (int i = 0; i < p.k; ++i) {
-            const int hs = ntt_stage_hs(p, i);
-            for (int b = threadIdx.x; b < T / 2; b += blockDim.x) ntt_phase_stage(p, t, s_lo, s_hi, hs, b);
-            __syncthreads();
+        if (ROUNDS) {
+            const int n_rounds = ntt_round_count(p);
+            for (int r = 0; r < n_rounds; ++r) {
+                const int slots = T >> ntt_round_size(p, r);
+                for (int s = threadIdx.x; s < slots; s += blockDim.x) ntt_phase_round_any(p, t, s_lo, s_hi, r, s);
+                __syncthreads();
+            }
+        } else {
+            for (int i = 0; i < p.k; ++i) {
+                const int hs = ntt_stage_hs(p, i);
+                for (int b = threadIdx.x; b < T / 2; b += blockDim.x) ntt_phase_stage(p, t, s_lo, s_hi, hs, b);
+                __syncthreads();
+            }
         }
         for (int e = threadIdx.x; e < T; e += blockDim.x) ntt_phase_store(p, t, data, s_lo, s_hi, e);
         __syncthreads();

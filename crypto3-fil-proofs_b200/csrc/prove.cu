@@ -14,24 +14,9 @@
 #include <vector>
 #include "msm_impl.cuh"
 #include "api_util.cuh"
+#include "pk.cuh"
 #include "ntt_kernels.cuh"
 #include "host_bls.hpp"
-
-namespace b2 {
-
-struct DevCsr { uint64_t n_rows = 0, nnz = 0; uint32_t* row_ptr = nullptr; uint32_t* col = nullptr; Fr* val = nullptr; };
-
-}  // namespace b2
-
-struct b2g16_pk {
-    uint32_t log_m = 0;
-    uint64_t n_cons = 0, n_in = 0, n_aux = 0, n_vars = 0, m = 0;
-    b2::DevCsr A, B, C;
-    b2::G1Affine *a = nullptr, *b_g1 = nullptr, *l = nullptr, *h = nullptr;
-    b2::G2Affine* b_g2 = nullptr;
-    b2::G1Affine alpha_g1, beta_g1, delta_g1;     // host copies, Montgomery
-    b2::G2Affine beta_g2, delta_g2;
-};
 
 namespace b2 {
 
@@ -205,7 +190,7 @@ static void host_g2_to_bytes(const G2Affine& p, uint8_t* b) {
 
 // ------------------------------------------------------------------------------ key load
 static void free_csr(DevCsr& m) { cudaFree(m.row_ptr); cudaFree(m.col); cudaFree(m.val); m = DevCsr(); }
-static void free_pk(b2g16_pk* pk) {
+void free_pk(b2g16_pk* pk) {
     if (!pk) return;
     free_csr(pk->A); free_csr(pk->B); free_csr(pk->C);
     cudaFree(pk->a); cudaFree(pk->b_g1); cudaFree(pk->b_g2); cudaFree(pk->l); cudaFree(pk->h);
@@ -227,7 +212,7 @@ static void load_csr(Ctx* c, const b2g16_csr& src, uint64_t n_cols, DevCsr& dst,
         fr_from_bytes_dev(c, reinterpret_cast<const uint8_t*>(dst.val), dst.val, src.nnz, d_bad);      // in place
     }
 }
-static b2g16_pk* new_pk_with_cs(Ctx* c, const b2g16_r1cs_view* cs, int* d_bad) {
+b2g16_pk* new_pk_with_cs(Ctx* c, const b2g16_r1cs_view* cs, int* d_bad) {
     B2_REQUIRE(cs && cs->log_m <= 30, B2G16_E_INVALID_ARG, "constraint system view");
     const uint64_t m = 1ull << cs->log_m;
     B2_REQUIRE(cs->n_cons + cs->n_in + 1 <= m, B2G16_E_INVALID_ARG, "domain too small: need n_cons + n_in + 1 <= 2^log_m");
@@ -244,6 +229,20 @@ static b2g16_pk* new_pk_with_cs(Ctx* c, const b2g16_r1cs_view* cs, int* d_bad) {
         load_csr(c, cs->C, pk->n_vars, pk->C, d_bad);
     } catch (...) { free_pk(pk); throw; }
     return pk;
+}
+// single elements: validate through the same device path as the queries, keep host copies
+void pk_set_single_points(Ctx* c, b2g16_pk* pk, const uint8_t* alpha_g1, const uint8_t* beta_g1, const uint8_t* delta_g1, const uint8_t* beta_g2,
+                          const uint8_t* delta_g2, int* d_bad) {
+    DevBuf<uint8_t> small(96 * 3 + 192 * 2, c->stream);
+    uint8_t hb[96 * 3 + 192 * 2];
+    memcpy(hb, alpha_g1, 96); memcpy(hb + 96, beta_g1, 96); memcpy(hb + 192, delta_g1, 96);
+    memcpy(hb + 288, beta_g2, 192); memcpy(hb + 480, delta_g2, 192);
+    B2_CUDA(cudaMemcpyAsync(small.get(), hb, sizeof(hb), cudaMemcpyHostToDevice, c->stream));
+    g1_from_bytes_dev(c, small.get(), (G1Affine*)small.get(), 3, d_bad, true);
+    g2_from_bytes_dev(c, small.get() + 288, (G2Affine*)(small.get() + 288), 2, d_bad, true);
+    B2_CUDA(cudaStreamSynchronize(c->stream));       // hb is on this frame
+    pk->alpha_g1 = host_g1_from_bytes(alpha_g1); pk->beta_g1 = host_g1_from_bytes(beta_g1); pk->delta_g1 = host_g1_from_bytes(delta_g1);
+    pk->beta_g2 = host_g2_from_bytes(beta_g2); pk->delta_g2 = host_g2_from_bytes(delta_g2);
 }
 template <class A> static A* upload_points(Ctx* c, const uint8_t* bytes, size_t n, int* d_bad) {
     A* d = nullptr;
@@ -543,17 +542,8 @@ int b2g16_pk_load(b2g16_ctx* hctx, const b2g16_pk_view* v, b2g16_pk** out) {
             pk->b_g2 = upload_points<G2Affine>(c, v->b_g2, pk->n_vars, bad.ptr());
             pk->l = upload_points<G1Affine>(c, v->l, pk->n_aux, bad.ptr());
             pk->h = upload_points<G1Affine>(c, v->h, pk->m - 1, bad.ptr());
-            // single elements: validate through the same device path, keep host copies
-            DevBuf<uint8_t> small(96 * 3 + 192 * 2, c->stream);
-            uint8_t hb[96 * 3 + 192 * 2];
-            memcpy(hb, v->alpha_g1, 96); memcpy(hb + 96, v->beta_g1, 96); memcpy(hb + 192, v->delta_g1, 96);
-            memcpy(hb + 288, v->beta_g2, 192); memcpy(hb + 480, v->delta_g2, 192);
-            B2_CUDA(cudaMemcpyAsync(small.get(), hb, sizeof(hb), cudaMemcpyHostToDevice, c->stream));
-            g1_from_bytes_dev(c, small.get(), (G1Affine*)small.get(), 3, bad.ptr(), true);
-            g2_from_bytes_dev(c, small.get() + 288, (G2Affine*)(small.get() + 288), 2, bad.ptr(), true);
+            pk_set_single_points(c, pk, v->alpha_g1, v->beta_g1, v->delta_g1, v->beta_g2, v->delta_g2, bad.ptr());
             bad.check("proving key");
-            pk->alpha_g1 = host_g1_from_bytes(v->alpha_g1); pk->beta_g1 = host_g1_from_bytes(v->beta_g1); pk->delta_g1 = host_g1_from_bytes(v->delta_g1);
-            pk->beta_g2 = host_g2_from_bytes(v->beta_g2); pk->delta_g2 = host_g2_from_bytes(v->delta_g2);
         } catch (...) { cudaStreamSynchronize(c->stream); free_pk(pk); throw; }
         *out = pk;
     });

@@ -157,6 +157,15 @@ def vk_file_read(path):
     return out
 
 
+def params_map(path):
+    """b2g16_params_map -> {name: (count, byte offset)} for ic, h, l, a, b_g1, b_g2."""
+    cnt, off = (C.c_uint64 * 6)(), (C.c_uint64 * 6)()
+    rc = load().b2g16_params_map(os.fsencode(path), cnt, off)
+    if rc != 0:
+        raise B2g16Error(rc, "b2g16_params_map(%s)" % path)
+    return {n: (int(cnt[i]), int(off[i])) for i, n in enumerate(("ic", "h", "l", "a", "b_g1", "b_g2"))}
+
+
 def csr_density(col, n_vars, n_always=0):
     """b2g16_query_density: bitmap (uint8, n_vars) of the variables whose query point is present, given the matrix's CSR
     column indices; n_always = n_in + 1 for the a query (input-consistency rows), 0 for b_g1 / b_g2."""
@@ -467,6 +476,15 @@ class Context:
         self._chk(load().b2g16_pk_load(self.h, C.byref(view), C.byref(h)))
         return ProvingKey(self, h, keep)
 
+    def pk_load_file(self, path, cs, want_vk=False):
+        """b2g16_pk_load_file: `.params` file streamed to the device (pinned ring, device-side conversion / expansion)."""
+        r1, keep = _r1cs_view(cs)
+        h = C.c_void_p()
+        vk = np.zeros(672 + 96 * (cs.n_in + 1), dtype=np.uint8) if want_vk else None
+        self._chk(load().b2g16_pk_load_file(self.h, os.fsencode(path), C.byref(r1), C.byref(h), _p(vk), C.c_size_t(vk.nbytes if want_vk else 0)))
+        pk = ProvingKey(self, h, keep)
+        return (pk, vk) if want_vk else pk
+
     def pk_generate(self, cs, toxic, want_vk=False):
         r1, keep = _r1cs_view(cs)
         h = C.c_void_p()
@@ -573,6 +591,56 @@ class Context:
 
     def synth_witness(self, pk, d_assignment_ptr, n_free):
         self._chk(load().b2g16_synth_witness(self.h, pk.h, C.c_void_p(d_assignment_ptr), C.c_uint64(n_free)))
+
+
+class MultiContext:
+    """b2g16_init_multi: several devices of one box driven from this process (one context + host thread per device)."""
+
+    def __init__(self, devices):
+        devs = (C.c_int * len(devices))(*devices)
+        self.h = C.c_void_p()
+        rc = load().b2g16_init_multi(devs, len(devices), C.byref(self.h))
+        if rc != 0:
+            raise B2g16Error(rc, "b2g16_init_multi(%s)" % list(devices))
+        self.n = len(devices)
+
+    def _chk(self, rc):
+        if rc != 0:
+            load().b2g16_multi_last_error.restype = C.c_char_p
+            raise B2g16Error(rc, (load().b2g16_multi_last_error(self.h) or b"").decode())
+
+    def close(self):
+        if self.h:
+            load().b2g16_shutdown_multi(self.h)
+            self.h = None
+
+    def key_generate_synth(self, log_m, n_in, n_free, seed, toxic, want_vk=False):
+        k = C.c_void_p()
+        vk = np.zeros(672 + 96 * (n_in + 1), dtype=np.uint8) if want_vk else None
+        self._chk(load().b2g16_mpk_generate_synth(self.h, C.c_uint32(log_m), C.c_uint64(n_in), C.c_uint64(n_free), C.c_uint64(seed), _p(_u8(toxic)),
+                                                 C.byref(k), _p(vk)))
+        return (k, vk) if want_vk else k
+
+    def key_load(self, key, cs):
+        v, keep = _pk_view(key, cs)
+        k = C.c_void_p()
+        self._chk(load().b2g16_mpk_load(self.h, C.byref(v), C.byref(k)))
+        return k
+
+    def key_free(self, k):
+        load().b2g16_mpk_free(self.h, k)
+
+    def prove(self, k, assignment, r, s):
+        out = np.zeros(192, dtype=np.uint8)
+        self._chk(load().b2g16_prove_multi(self.h, k, _p(_u8(assignment)), _p(_u8(r)), _p(_u8(s)), 0, _p(out)))
+        return bytes(out)
+
+    def prove_batch(self, k, assignments, rs, ss):
+        a = _u8(assignments)
+        n = len(rs)
+        out = np.zeros(192 * n, dtype=np.uint8)
+        self._chk(load().b2g16_prove_batch_multi(self.h, k, _p(a), C.c_size_t(n), _p(_u8(rs)), _p(_u8(ss)), 0, _p(out)))
+        return [bytes(out[192 * i:192 * (i + 1)]) for i in range(n)]
 
 
 def _r1cs_view(cs):

@@ -203,6 +203,34 @@ int b2g16_prove_assemble(b2g16_ctx*, const b2g16_pk*, const uint8_t* partials, u
 int b2g16_prove_batch(b2g16_ctx*, const b2g16_pk*, const uint8_t* assignments32, size_t n_partitions,
                       const uint8_t* r32s, const uint8_t* s32s, int priority, uint8_t* proofs_out);
 
+/* ---- several GPUs of one box from one process.  The reference's caller is a single C++ process that hands every
+ *      partition of a proof to one prover call (compound_proof::circuit_proofs, S/core/proof/compound_proof.hpp:89-95,
+ *      127-137; F/api/seal.hpp:298-308, F/api/post.hpp:305-348): these entry points spread that call over the devices
+ *      given to b2g16_init_multi, one context and one host thread per device, no torch.distributed and no NCCL (the only
+ *      exchange is 576 bytes of partial sums per device and proof, which come back through the host).
+ *   b2g16_prove_batch_multi: partition p of a full wave runs on device p mod n; the last, partial wave splits the devices
+ *      into one group per remaining partition and every group proves its partition in latency mode.  Proofs are written
+ *      in partition order; each equals what b2g16_prove returns for the same inputs.
+ *   b2g16_prove_multi: one proof over all n devices in latency mode (b2g16_prove_partial on every device + assemble).
+ * The same device may be listed more than once (two contexts share it): that is how a single-GPU box tests the schedule.
+ * Keys are replicated: b2g16_mpk_load / _generate_synth build one resident key per context. */
+typedef struct b2g16_mctx b2g16_mctx;
+typedef struct b2g16_mpk b2g16_mpk;
+int b2g16_init_multi(const int* devices, int n, b2g16_mctx** out);
+int b2g16_shutdown_multi(b2g16_mctx*);
+int b2g16_multi_count(const b2g16_mctx*);
+b2g16_ctx* b2g16_multi_ctx(b2g16_mctx*, int slot);           /* the per-device context, e.g. for b2g16_vk_prepare */
+const char* b2g16_multi_last_error(b2g16_mctx*);              /* first failure of the last multi call, with its device */
+int b2g16_mpk_load(b2g16_mctx*, const b2g16_pk_view*, b2g16_mpk** out);
+int b2g16_mpk_generate_synth(b2g16_mctx*, uint32_t log_m, uint64_t n_in, uint64_t n_free, uint64_t seed, const uint8_t toxic[160],
+                             b2g16_mpk** out, uint8_t* vk_out);
+b2g16_pk* b2g16_mpk_device_key(const b2g16_mpk*, int slot);
+int b2g16_mpk_free(b2g16_mctx*, b2g16_mpk*);
+int b2g16_prove_multi(b2g16_mctx*, const b2g16_mpk*, const uint8_t* assignment32, const uint8_t r32[32], const uint8_t s32[32], int priority,
+                      uint8_t proof_out[192]);
+int b2g16_prove_batch_multi(b2g16_mctx*, const b2g16_mpk*, const uint8_t* assignments32, size_t n_partitions, const uint8_t* r32s,
+                            const uint8_t* s32s, int priority, uint8_t* proofs_out);
+
 /* Same prover when the caller's circuit synthesis already produced the constraint evaluations
  * (the bellperson-style flow of compound_proof::circuit_proofs, S/core/proof/compound_proof.hpp:127-137:
  * synthesize -> a, b, c on the domain -> prove): a32 / b32 / c32 are 2^log_m canonical scalars each
@@ -268,6 +296,19 @@ int b2g16_query_expand(const uint8_t* filtered, uint64_t n_filtered, const uint8
                        uint8_t* dense_out);
 int b2g16_query_filter(const uint8_t* dense, uint64_t n_vars, size_t point_bytes, uint8_t* filtered_out, uint8_t* density_out,
                        uint64_t* count_out);
+
+/* ---- mapped / streamed parameter load (S/core/crypto/mapped_scheme_params.hpp:43-84, S/core/parameter_cache.hpp:125-129).
+ *   b2g16_params_map   : counts and byte offsets of the six arrays of a `.params` file in file order
+ *                        { ic, h, l, a, b_g1, b_g2 } -- the offset tables build_mapped_parameters keeps; reads the
+ *                        length prefixes only.
+ *   b2g16_pk_load_file : file -> resident key.  The queries stream through a ring of pinned host buffers
+ *                        (tuning key "key_chunk_mib", default 32) and are converted on the device (big-endian
+ *                        coordinates -> Montgomery limbs, range / curve checks); density-filtered a / b_g1 / b_g2
+ *                        queries are expanded on the device with the column occupancy of cs->A / cs->B (plus ONE and
+ *                        the public inputs for a), so the key never exists in host memory.  vk_out (optional,
+ *                        672 + 96 (n_in + 1) bytes): the vk block in the b2g16_vk_prepare layout. */
+int b2g16_params_map(const char* path, uint64_t counts[6], uint64_t offsets[6]);
+int b2g16_pk_load_file(b2g16_ctx*, const char* path, const b2g16_r1cs_view* cs, b2g16_pk** out, uint8_t* vk_out, size_t vk_bytes);
 
 /* ---- parameter-cache entries: the naming and the two small files of S/core/parameter_cache.hpp.
  *   b2g16_cache_dir        : $FIL_PROOFS_PARAMETER_CACHE, else /var/tmp/filecoin-proof-parameters        (:52-53,65-71)

@@ -127,6 +127,7 @@ struct EmuDomain {
         return t;
     }
 };
+static bool g_emu_ntt_rounds = true;    // register rounds (what the kernel runs) or one stage at a time (the reference form)
 static void run_step(const NttStep& s) {
     const NttPass& p = s.pass;
     const int T = 1 << (p.k + p.logc);
@@ -134,13 +135,18 @@ static void run_step(const NttStep& s) {
     for (uint64_t tile = 0; tile < ntt_pass_tiles(p); ++tile) {
         NttTile t = ntt_make_tile(p, tile);
         for (int e = 0; e < T; ++e) ntt_phase_load(p, t, s.src, lo.data(), hi.data(), e);
-        for (int i = 0; i < p.k; ++i) for (int b = 0; b < T / 2; ++b) ntt_phase_stage(p, t, lo.data(), hi.data(), ntt_stage_hs(p, i), b);
+        if (g_emu_ntt_rounds) {
+            for (int r = 0; r < ntt_round_count(p); ++r) for (int sl = 0; sl < (T >> ntt_round_size(p, r)); ++sl) ntt_phase_round_any(p, t, lo.data(), hi.data(), r, sl);
+        } else {
+            for (int i = 0; i < p.k; ++i) for (int b = 0; b < T / 2; ++b) ntt_phase_stage(p, t, lo.data(), hi.data(), ntt_stage_hs(p, i), b);
+        }
         for (int e = 0; e < T; ++e) ntt_phase_store(p, t, s.dst, lo.data(), hi.data(), e);
     }
 }
 extern "C" {
 static bool g_emu_tw_tables = true;
 void emu_set_tw_tables(int on) { g_emu_tw_tables = on != 0; }
+void emu_set_ntt_rounds(int on) { g_emu_ntt_rounds = on != 0; }
 int emu_ntt(uint8_t* data, unsigned log_n, int inverse, int coset) {
     EmuDomain d((int)log_n, g_emu_tw_tables);
     size_t n = (size_t)1 << log_n;

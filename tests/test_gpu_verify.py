@@ -150,3 +150,53 @@ def test_prove_abc_and_params_file(ctx, oracle, tmp_path):
     pvk = ctx.vk_prepare(back["vk"])
     assert ctx.verify(pvk, z[1:1 + s.n_in], got)
     pvk.free(); pk2.free()
+
+
+def test_streamed_key_load_from_file(ctx, oracle, tmp_path):
+    """b2g16_pk_load_file: the `.params` cache entry streamed to the device (pinned ring, device-side byte order /
+    Montgomery conversion, device-side expansion of density-filtered queries) gives the same resident key -- hence the same
+    192 proof bytes -- as b2g16_pk_load from host arrays, for a dense file and for a bellman-style filtered one.
+    (mapped_scheme_params.hpp:43-84, parameter_cache.hpp:125-129)"""
+    s, cs, z = util.synth_instance(oracle, 10, 3, seed=57)
+    toxic, r, sr = util.toxic_from_seed(57)
+    pk, vk = ctx.pk_generate(cs, toxic, want_vk=True)
+    m, nv = 1 << s.log_m, cs.n_vars
+    params = {"gamma_g2": vk[288:480], "ic": vk[672:].reshape(-1, 96)}
+    for which, n, cnt in ((0, "a", nv), (1, "b_g1", nv), (2, "b_g2", nv), (3, "l", cs.n_aux), (4, "h", m - 1)):
+        params[n] = pk.export(which, cnt)
+    for which, n in ((5, "alpha_g1"), (6, "beta_g1"), (7, "delta_g1"), (8, "beta_g2"), (9, "delta_g2")):
+        params[n] = pk.export(which, 1)[0]
+    want = ctx.prove(pk, z, r, sr)
+    pk.free()
+    dense_path, filt_path = str(tmp_path / "dense.params"), str(tmp_path / "filtered.params")
+    lib.params_write(dense_path, params)
+    filt = dict(params)
+    kept = {}
+    for n, w in (("a", 96), ("b_g1", 96), ("b_g2", 192)):
+        filt[n], _ = lib.query_filter(params[n], w)
+        kept[n] = len(filt[n])
+    assert kept["a"] < nv and kept["b_g1"] == kept["b_g2"] < nv      # the synthetic instance has empty columns
+    lib.params_write(filt_path, filt)
+    mp = lib.params_map(filt_path)
+    assert mp["ic"] == (cs.n_in + 1, 868) and mp["h"][0] == m - 1 and mp["a"][0] == kept["a"] and mp["b_g2"][0] == kept["b_g2"]
+    assert mp["h"][1] == 868 + 96 * (cs.n_in + 1) + 4
+    ctx.set_tuning("key_chunk_mib", 1)                               # several ring turns even at this size
+    for path in (dense_path, filt_path):
+        pk2, vk2 = ctx.pk_load_file(path, cs, want_vk=True)
+        assert np.array_equal(vk2, vk)
+        for which, n, cnt in ((0, "a", nv), (1, "b_g1", nv), (2, "b_g2", nv), (3, "l", cs.n_aux), (4, "h", m - 1)):
+            assert np.array_equal(pk2.export(which, cnt), params[n]), (path, n)
+        assert ctx.prove(pk2, z, r, sr) == want
+        pk2.free()
+    ctx.set_tuning("key_chunk_mib", 32)
+    # a corrupted coordinate (not on the curve) and a truncated file are errors
+    raw = bytearray(open(dense_path, "rb").read())
+    raw[mp["h"][1] + 96 * 5 + 95] ^= 1
+    bad_path = str(tmp_path / "bad.params")
+    open(bad_path, "wb").write(raw)
+    with pytest.raises(lib.B2g16Error) as e:
+        ctx.pk_load_file(bad_path, cs)
+    assert e.value.code in (-2, -3)
+    open(bad_path, "wb").write(bytes(raw[:-50]))
+    with pytest.raises(lib.B2g16Error):
+        ctx.pk_load_file(bad_path, cs)

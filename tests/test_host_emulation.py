@@ -169,12 +169,14 @@ def emu2():
 
 @pytest.mark.parametrize("log_n", [0, 1, 2, 5, 11, 12, 13, 14])
 @pytest.mark.parametrize("inverse,coset", [(0, 0), (1, 0), (0, 1), (1, 1)])
-@pytest.mark.parametrize("tw_tables", [1, 0])
-def test_ntt_passes_vs_oracle(emu2, oracle, log_n, inverse, coset, tw_tables):
+@pytest.mark.parametrize("tw_tables,rounds", [(1, 1), (0, 1), (1, 0)])
+def test_ntt_passes_vs_oracle(emu2, oracle, log_n, inverse, coset, tw_tables, rounds):
     """tw_tables = 1: strided passes take combined butterfly twiddles from per-pass root tables (no inter-pass twiddle);
-    0: the fallback that rebuilds inter-pass twiddles as tlo * thi."""
+    0: the fallback that rebuilds inter-pass twiddles as tlo * thi.  rounds = 1: three stages at a time on eight elements
+    in registers (ntt_phase_round, what the kernel runs); 0: one stage at a time (ntt_phase_stage, the reference form)."""
     if not tw_tables and log_n <= 11:
         pytest.skip("single contiguous pass: no strided pass to differ")
+    emu2.emu_set_ntt_rounds(rounds)
     rng = np.random.Generator(np.random.PCG64(1000 + log_n))
     x = codec.random_fr(1 << log_n, rng)
     got = x.copy()
@@ -183,6 +185,7 @@ def test_ntt_passes_vs_oracle(emu2, oracle, log_n, inverse, coset, tw_tables):
         n_pass = emu2.emu_ntt(_p(got), C.c_uint(log_n), inverse, coset)
     finally:
         emu2.emu_set_tw_tables(1)
+        emu2.emu_set_ntt_rounds(1)
     assert n_pass == (1 if log_n <= 11 else 2)
     want = oracle.ntt(x, inverse=bool(inverse), coset=bool(coset))
     assert np.array_equal(got, want)

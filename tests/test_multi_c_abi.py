@@ -1,0 +1,65 @@
+"""Several devices behind the C ABI (b2g16_init_multi / b2g16_prove_batch_multi / b2g16_prove_multi, csrc/multi.cu):
+the partition loop of compound_proof::prove
+(libs/storage/include/nil/filecoin/storage/proofs/core/proof/compound_proof.hpp:89-95,127-137) spread over the box's
+GPUs from ONE process.  The schedule is checked on however many devices the lease has; with one device the same
+device is listed several times (each entry gets its own context, stream and host thread), which exercises the full
+waves, the latency-mode remainder wave and the assembly exactly as separate devices would."""
+import numpy as np
+import pytest
+
+from b2g16 import lib
+import util
+
+
+def test_init_multi_without_a_device_is_an_error():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a CUDA device is present")
+    with pytest.raises(lib.B2g16Error) as e:
+        lib.MultiContext([0, 1])
+    assert e.value.code == -4            # B2G16_E_CUDA: no CPU fallback
+    with pytest.raises(lib.B2g16Error) as e:
+        lib.MultiContext([])
+    assert e.value.code == -1
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("slots,n_part", [(2, 5), (3, 4), (4, 2), (1, 2)])
+def test_prove_batch_multi_equals_single_device(oracle, slots, n_part):
+    import torch
+    n_dev = torch.cuda.device_count()
+    devices = [i % n_dev for i in range(slots)]
+    log_m, n_in, n_free, seed = 12, 5, 8, 99
+    toxic, _, _ = util.toxic_from_seed(seed)
+    rng = np.random.Generator(np.random.PCG64(seed))
+    from b2g16 import codec
+    rs, ss = codec.random_fr(n_part, rng), codec.random_fr(n_part, rng)
+
+    # single-device reference proofs, one witness per partition (different inputs / free variables)
+    ctx = lib.Context(0)
+    pk, vk = ctx.pk_generate_synth(log_m, n_in, n_free, seed, toxic, want_vk=True)
+    nv = pk.shape()["n_vars"]
+    zs = np.zeros((n_part, nv, 32), dtype=np.uint8)
+    want = []
+    for p in range(n_part):
+        dz = torch.zeros((nv, 32), dtype=torch.uint8, device="cuda:0")
+        head = codec.random_fr(1 + n_in + n_free, rng); head[0] = 0; head[0, 0] = 1
+        dz[: head.shape[0]] = torch.from_numpy(head).cuda()
+        ctx.synth_witness(pk, dz.data_ptr(), n_free)
+        zs[p] = dz.cpu().numpy()
+        want.append(ctx.prove(pk, zs[p], rs[p], ss[p]))
+    pvk = ctx.vk_prepare(vk)
+    assert all(ctx.verify(pvk, zs[p][1:1 + n_in], want[p]) for p in range(n_part))
+    pvk.free(); pk.free(); ctx.close()
+
+    m = lib.MultiContext(devices)
+    k = m.key_generate_synth(log_m, n_in, n_free, seed, toxic)
+    got = m.prove_batch(k, zs, rs, ss)
+    assert got == want                                       # partition order, bit-exact
+    assert m.prove(k, zs[0], rs[0], ss[0]) == want[0]        # one proof over all contexts (latency mode)
+    bad = zs[:1].copy(); bad[0, 3, :] = 0xFF                 # non-canonical scalar: error with the device named, no proof
+    with pytest.raises(lib.B2g16Error) as e:
+        m.prove_batch(k, bad, rs[:1], ss[:1])
+    assert e.value.code == -2 and "device" in str(e.value)
+    m.key_free(k)
+    m.close()
