@@ -442,21 +442,26 @@ def proof_roofline(ctx, prove_fn, want_proof, log_m, mad_peak, hbm_peak, peak_sr
     e = h[-1]
     g2 = [x for x in log if x["group"] == 2]
     achieved = n_h * MAD32_PER_G1_POINT / (e["ms"] * 1e-3) / 1e12
-    kname = {1: "msm_accumulate_chunked_kernel<Fq,128,2>", 2: "msm_accumulate_kernel<Fq2,64,1,0> (<= 16-bit windows) / msm_accumulate_chunked_kernel<Fq2,64,4>"}
-    roofline = {"kernel": kname[1] + " -- bucket accumulation of the H query, timed inside a proof (multiexps serialised for this one proof)",
+    kname = {1: "tree_down0_kernel<Fq> + tree_up0_kernel<Fq> (batched-affine tree levels, ~85 % of the stage) + msm_accumulate_chunked_kernel<Fq,128,2,direct> (XYZZ tail)",
+             2: "tree_down0_kernel<Fq2> + tree_up0_kernel<Fq2> + msm_accumulate_chunked_kernel<Fq2,64,4,direct>"}
+    # what the stage really executes: an affine addition with a shared inversion is 6 field products (G1: 6 x 300 MAD32;
+    # G2: 5 lazy-reduction Fq2 products of 744 + one Fq2 squaring of 600 = 4320), not the 10 / 30 of the mixed XYZZ addition
+    # that SURVEY's per-point figure assumes -- so `frac`, which keeps SURVEY's algorithmic work as the numerator, can
+    # exceed the share of the multiplier the stage keeps busy, reported beside it as pipe_utilisation_actual.
+    roofline = {"kernel": kname[1] + " -- bucket accumulation stage of the H query, timed inside a proof (multiexps serialised for this one proof)",
                 "bound": "int32-imad", "achieved": achieved, "peak": mad_peak / 1e12, "unit": "TMAD32/s", "frac": achieved / (mad_peak / 1e12),
                 "traffic": ncu_traffic(log_m),
-                "traffic_note": "DRAM bytes per accumulate launch from the committed ncu --set full capture of the same kernel at 2^22 (profiles/); the windows' gathers of 96-byte points are the kernel's own minimum, SURVEY's N*128 B counts one read of the inputs",
+                "traffic_note": "DRAM bytes of the whole accumulation stage of one 2^22 G1 multiexp (all its launches) from the committed ncu --set full capture (profiles/r02_ncu_full_msm_g1_2p22.json); every tree level re-reads its entries twice (prefix pass + addition pass), SURVEY's N*128 B counts one read of the inputs",
                 "launch_ms": e["ms"], "units_per_launch": n_h, "window_bits": e["c"], "additions_in_launch": e["entries"],
                 "alg_mad32_per_point": MAD32_PER_G1_POINT,
-                "actual_mad32_per_addition": 3000, "pipe_utilisation_actual": e["entries"] * 3000.0 / (e["ms"] * 1e-3) / mad_peak,
+                "actual_mad32_per_addition": 1800, "pipe_utilisation_actual": e["entries"] * 1800.0 / (e["ms"] * 1e-3) / mad_peak,
                 "peak_source": "b2g16_measure_mad32_peak (dependency-free mad.wide.u32 loop, this run)",
                 "hbm_view": {"alg_bytes": n_h * 128, "GBps": n_h * 128 / (e["ms"] * 1e-3) / 1e9, "peak_GBps": hbm_peak, "peak_source": peak_src}}
     if g2:
         x = g2[-1]
         roofline["g2_launch"] = {"kernel": kname[2], "launch_ms": x["ms"], "window_bits": x["c"], "additions_in_launch": x["entries"], "bases_in_slice": x["n"],
-                                 "pipe_utilisation_actual": x["entries"] * 9000.0 / (x["ms"] * 1e-3) / mad_peak,
-                                 "note": "b_g2 query: identity bases and zero scalars take no slot, so the additions, not the slice length, are the work; 30 Fq products = 9000 MAD32 per Fq2 mixed addition"}
+                                 "actual_mad32_per_addition": 4320, "pipe_utilisation_actual": x["entries"] * 4320.0 / (x["ms"] * 1e-3) / mad_peak,
+                                 "note": "b_g2 query: identity bases and zero scalars take no slot, so the additions, not the slice length, are the work"}
     return roofline, log
 
 
@@ -806,20 +811,13 @@ def msm_linearity_check(ctx, torch, dev, kk, sc, n, res, extra_dot=None):
 
 
 def ncu_traffic(log_m):
-    """dram__bytes_read.sum + dram__bytes_write.sum of one accumulate launch from the committed
-    `ncu --set full` capture (profiles/r01_ncu_full_s13.json: G1 MSM at 2^22); null at other sizes."""
-    path = os.path.join(ROOT, "profiles", "r01_ncu_full_s13.json")
+    """dram__bytes_read.sum + dram__bytes_write.sum over the accumulation-stage launches of one 2^22 G1 multiexp, from the
+    committed `ncu --set full` capture (profiles/r02_ncu_full_msm_g1_2p22.json, written by tools/ncu_stage_summary.py);
+    null at other sizes."""
+    path = os.path.join(ROOT, "profiles", "r02_ncu_full_msm_g1_2p22.json")
     if log_m != 22 or not os.path.exists(path):
         return None
-    scale = {"Gbyte": 1e9, "Mbyte": 1e6, "Kbyte": 1e3, "byte": 1.0}
-    for l in json.load(open(path))["launches"]:
-        if "msm_accumulate" in l.get("Kernel Name", ""):
-            tot = 0.0
-            for k, v in l.items():
-                if k.startswith("dram__bytes_read.sum") or k.startswith("dram__bytes_write.sum"):
-                    tot += float(v) * scale[k.split("[")[1].rstrip("]")]
-            return tot
-    return None
+    return float(json.load(open(path))["total_dram_bytes"])
 
 
 def main():

@@ -7,8 +7,8 @@
 
 namespace b2 {
 
-template <class Fn> int guard(Ctx* c, Fn&& fn) {
-    std::lock_guard<std::mutex> lock(c->mu);
+template <class Fn> int guard(Ctx* c, Fn&& fn, bool priority = false) {
+    ContextGate gate(c, priority);
     try {
         cudaSetDevice(c->device);
         fn();

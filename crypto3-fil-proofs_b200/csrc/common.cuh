@@ -4,6 +4,7 @@
 #include <stdint.h>
 #include <stdio.h>
 #include <map>
+#include <condition_variable>
 #include <mutex>
 #include <string>
 #include <vector>
@@ -22,7 +23,13 @@ struct Ctx {
     cudaStream_t aux[4] = {nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t ev_fork = nullptr, ev_join[4] = {nullptr, nullptr, nullptr, nullptr};
     std::string last_error;
+    // Queue of the context: one call in flight at a time; a waiting priority call (the `priority` flag of
+    // compound_proof::circuit_proofs, compound_proof.hpp:134 -- PoSt proofs jump ahead of sealing proofs) is admitted
+    // before any waiting ordinary call (ContextGate below).
     std::mutex mu;
+    std::condition_variable cv;
+    bool busy = false;
+    int hi_waiting = 0;
     Fr* roots_fwd = nullptr;            // w_{2^11}^j, j < 1024
     Fr* roots_inv = nullptr;
     std::map<int, NttDomain*> domains;
@@ -48,6 +55,24 @@ struct Ctx {
     bool klog_on = false;
     std::vector<KernelLogEntry> klog;
     uint32_t* d_klog_entries = nullptr;                   // sorted (point, window) entries of each logged launch, 64 slots
+};
+
+// RAII admission to a context: blocks while another call runs; ordinary calls also yield to waiting priority calls.
+struct ContextGate {
+    Ctx* c;
+    ContextGate(Ctx* ctx, bool priority) : c(ctx) {
+        std::unique_lock<std::mutex> l(c->mu);
+        if (priority) ++c->hi_waiting;
+        c->cv.wait(l, [&] { return !c->busy && (priority || c->hi_waiting == 0); });
+        if (priority) --c->hi_waiting;
+        c->busy = true;
+    }
+    ~ContextGate() {
+        { std::lock_guard<std::mutex> l(c->mu); c->busy = false; }
+        c->cv.notify_all();
+    }
+    ContextGate(const ContextGate&) = delete;
+    ContextGate& operator=(const ContextGate&) = delete;
 };
 
 struct CudaError { cudaError_t e; const char* what; const char* file; int line; };

@@ -82,10 +82,48 @@ template <class F> B2_HD Affine<F> tree_entry(const TreeIn<F>& in, uint32_t e) {
     }
     return tree_ld_affine(in.pts + e);
 }
+// L2 prefetch of entry e (first and last byte: a 96 / 192-byte point may straddle 128-byte lines).  The big level kernels
+// walk their outputs serially; without it every iteration starts with a DRAM-latency stall that two to four warps per
+// scheduler cannot cover (level 0 gathers random key points).
+template <class F> B2_HD void tree_prefetch_entry(const TreeIn<F>& in, uint32_t e, bool x_only) {
+#if defined(__CUDA_ARCH__)
+    const char* q = reinterpret_cast<const char*>(in.sorted ? in.bases + (in.sorted[e] & 0x7fffffffu) : in.pts + e);
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(q));
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(q + (x_only ? sizeof(F) : sizeof(Affine<F>)) - 4));
+#else
+    (void)in; (void)e; (void)x_only;
+#endif
+}
 // x coordinate of entry e alone (the sign bit of a level-0 reference does not touch x)
 template <class F> B2_HD F tree_entry_x(const TreeIn<F>& in, uint32_t e) {
     if (in.sorted) return tree_ld_field(&in.bases[in.sorted[e] & 0x7fffffffu].x);
     return tree_ld_field(&in.pts[e].x);
+}
+
+// Products of the fast path of tree_down0: inlined for both fields.  Fq2::operator* is an out-of-line call whose
+// operands and result travel through local memory -- fine for the rare branches, too slow for the loop that does
+// ~90 % of a G2 multiexp's arithmetic (-DB2_TREE_INLINE_FQ2=0 restores the calls for comparison).
+#ifndef B2_TREE_INLINE_FQ2
+#define B2_TREE_INLINE_FQ2 1
+#endif
+B2_HD Fq tree_mul(const Fq& a, const Fq& b) { return a * b; }
+B2_HD Fq tree_sqr(const Fq& a) { return a.sqr(); }
+#if B2_TREE_INLINE_FQ2
+B2_HD Fq2 tree_mul(const Fq2& a, const Fq2& b) { return wide::fq2_mul_lazy<false>(a, b); }
+B2_HD Fq2 tree_sqr(const Fq2& a) { return a.sqr_inline(); }
+#else
+B2_HD Fq2 tree_mul(const Fq2& a, const Fq2& b) { return a * b; }
+B2_HD Fq2 tree_sqr(const Fq2& a) { return a.sqr(); }
+#endif
+
+// y coordinate of entry e, sign of a level-0 reference applied (the entry is known not to be the identity)
+template <class F> B2_HD F tree_entry_y(const TreeIn<F>& in, uint32_t e) {
+    if (in.sorted) {
+        const uint32_t ix = in.sorted[e];
+        const F y = tree_ld_field(&in.bases[ix & 0x7fffffffu].y);
+        return (ix >> 31) ? y.neg() : y;
+    }
+    return tree_ld_field(&in.pts[e].y);
 }
 
 // What one output of a level is.  KIND_ADD / KIND_DBL need the inverse of `d`.
@@ -127,6 +165,7 @@ template <class F> B2_HD void tree_up0_body(const TreeIn<F>& in, const uint32_t*
         const uint32_t i0 = in.off[b] + 2 * (o - off_out[b]);
         const bool has_pair = i0 + 1 < in.off[b + 1];
         tree_st_field(pp + o, prod);
+        if (o + 1 < o_end && o + 1 < next && i0 + 3 < in.off[b + 1]) { tree_prefetch_entry(in, i0 + 2, true); tree_prefetch_entry(in, i0 + 3, true); }
         if (!has_pair) continue;
         // The denominator of an ordinary addition needs the two x coordinates only (half the bytes of the gather):
         // x != 0 rules out the identity, x0 != x1 the doubling / cancellation cases; everything else takes the full path.
@@ -191,22 +230,41 @@ template <class F> B2_HD void tree_down0_body(const TreeIn<F>& in, const uint32_
         while (o < first) { --b; first = off_out[b]; }
         const uint32_t i0 = in.off[b] + 2 * (o - first);
         const bool has_pair = i0 + 1 < in.off[b + 1];
-        const Affine<F> p0 = tree_entry(in, i0);
-        Affine<F> r = p0;
+        if (o > (uint32_t)o0 && o > first) { tree_prefetch_entry(in, i0 - 2, false); tree_prefetch_entry(in, i0 - 1, false); }   // output o - 1, same bucket
+        Affine<F> r;
+        bool done = false;
         if (has_pair) {
-            const Affine<F> p1 = tree_entry(in, i0 + 1);
-            F d;
-            const int kind = tree_classify(p0, p1, true, d);
-            if (kind == TREE_COPY1) r = p1;
-            else if (kind == TREE_ZERO) r = Affine<F>::identity();
-            else if (kind != TREE_COPY0) {
-                const F inv_d = I * tree_ld_field(pp + o);
-                I = I * d;
-                F lam;
-                if (kind == TREE_ADD) lam = (p1.y - p0.y) * inv_d;
-                else { const F xx = p0.x.sqr(); lam = (xx.dbl() + xx) * inv_d; }
-                r.x = lam.sqr() - p0.x - p1.x;           // doubling: p1.x == p0.x
-                r.y = lam * (p0.x - r.x) - p0.y;
+            // ordinary addition (both x non-zero and different -- the same test as in up0): the coordinates are fetched
+            // when they are needed and dropped as soon as they are used, which keeps the G2 form's live state at five
+            // field elements instead of nine
+            const F x0 = tree_entry_x(in, i0), x1 = tree_entry_x(in, i0 + 1);
+            if (!x0.is_zero() && !x1.is_zero() && x0 != x1) {
+                F lam = tree_mul(I, tree_ld_field(pp + o));  // 1 / (x1 - x0)
+                I = tree_mul(I, x1 - x0);
+                lam = tree_mul(tree_entry_y(in, i0 + 1) - tree_entry_y(in, i0), lam);
+                r.x = tree_sqr(lam) - x0 - x1;
+                r.y = tree_mul(lam, x0 - r.x) - tree_entry_y(in, i0);
+                done = true;
+            }
+        }
+        if (!done) {
+            const Affine<F> p0 = tree_entry(in, i0);
+            r = p0;
+            if (has_pair) {
+                const Affine<F> p1 = tree_entry(in, i0 + 1);
+                F d;
+                const int kind = tree_classify(p0, p1, true, d);
+                if (kind == TREE_COPY1) r = p1;
+                else if (kind == TREE_ZERO) r = Affine<F>::identity();
+                else if (kind != TREE_COPY0) {
+                    const F inv_d = I * tree_ld_field(pp + o);
+                    I = I * d;
+                    F lam;
+                    if (kind == TREE_ADD) lam = (p1.y - p0.y) * inv_d;
+                    else { const F xx = p0.x.sqr(); lam = (xx.dbl() + xx) * inv_d; }
+                    r.x = lam.sqr() - p0.x - p1.x;           // doubling: p1.x == p0.x
+                    r.y = lam * (p0.x - r.x) - p0.y;
+                }
             }
         }
         out[o] = r;
@@ -222,7 +280,7 @@ template <class F> B2_HD void tree_down0_body(const TreeIn<F>& in, const uint32_
 #ifndef B2_TREE_G2_MINB
 #define B2_TREE_G2_MINB 1
 #endif
-template <class F> struct TreeMinBlocks { static constexpr int value = sizeof(F) > 48 ? B2_TREE_G2_MINB : 1; };
+template <class F> struct TreeMinBlocks { static constexpr int value = sizeof(F) > 48 ? B2_TREE_G2_MINB : 4; };   // G1: 128 registers, four CTAs per SM
 template <class F> __global__ void __launch_bounds__(128, TreeMinBlocks<F>::value) tree_up0_kernel(TreeIn<F> in, const uint32_t* __restrict__ off_out, uint32_t n_buckets, uint32_t K,
                                                                           F* __restrict__ pp, F* __restrict__ tot) {
     tree_up0_body<F>(in, off_out, n_buckets, K, blockIdx.x * blockDim.x + threadIdx.x, pp, tot);

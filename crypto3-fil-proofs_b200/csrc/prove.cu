@@ -590,27 +590,24 @@ int b2g16_pk_export(b2g16_ctx* hctx, const b2g16_pk* pk, int which, uint8_t* out
 
 int b2g16_prove_device(b2g16_ctx* hctx, const b2g16_pk* pk, const uint8_t* d_assignment32, const uint8_t r32[32], const uint8_t s32[32],
                        int priority, uint8_t proof_out[192], b2g16_trace* trace) {
-    (void)priority;   // one in-flight proof per context: the guard mutex is the queue (compound_proof.hpp:134 hint)
     Ctx* c = reinterpret_cast<Ctx*>(hctx);
     if (!c || !pk || !d_assignment32 || !r32 || !s32 || !proof_out) return B2G16_E_INVALID_ARG;
-    return guard(c, [&] { prove_one(c, pk, d_assignment32, r32, s32, proof_out, trace); });
+    return guard(c, [&] { prove_one(c, pk, d_assignment32, r32, s32, proof_out, trace); }, priority != 0);
 }
 
 int b2g16_prove(b2g16_ctx* hctx, const b2g16_pk* pk, const uint8_t* assignment32, const uint8_t r32[32], const uint8_t s32[32],
                 int priority, uint8_t proof_out[192], b2g16_trace* trace) {
-    (void)priority;
     Ctx* c = reinterpret_cast<Ctx*>(hctx);
     if (!c || !pk || !assignment32 || !r32 || !s32 || !proof_out) return B2G16_E_INVALID_ARG;
     return guard(c, [&] {
         DevBuf<uint8_t> dz(pk->n_vars * 32, c->stream);
         B2_CUDA(cudaMemcpyAsync(dz.get(), assignment32, pk->n_vars * 32, cudaMemcpyHostToDevice, c->stream));
         prove_one(c, pk, dz.get(), r32, s32, proof_out, trace);
-    });
+    }, priority != 0);
 }
 
 int b2g16_prove_abc(b2g16_ctx* hctx, const b2g16_pk* pk, const uint8_t* a32, const uint8_t* b32, const uint8_t* c32, const uint8_t* assignment32,
                     const uint8_t r32[32], const uint8_t s32[32], int priority, uint8_t proof_out[192], b2g16_trace* trace) {
-    (void)priority;
     Ctx* c = reinterpret_cast<Ctx*>(hctx);
     if (!c || !pk || !a32 || !b32 || !c32 || !assignment32 || !r32 || !s32 || !proof_out) return B2G16_E_INVALID_ARG;
     return guard(c, [&] {
@@ -618,7 +615,7 @@ int b2g16_prove_abc(b2g16_ctx* hctx, const b2g16_pk* pk, const uint8_t* a32, con
         B2_CUDA(cudaMemcpyAsync(dz.get(), assignment32, pk->n_vars * 32, cudaMemcpyHostToDevice, c->stream));
         const uint8_t* abc[3] = {a32, b32, c32};
         prove_one(c, pk, dz.get(), r32, s32, proof_out, trace, abc);
-    });
+    }, priority != 0);
 }
 
 // One proof over `parts` GPUs (latency mode): each rank, holding the whole key and witness,
@@ -706,17 +703,20 @@ int b2g16_prove_assemble(b2g16_ctx* hctx, const b2g16_pk* pk, const uint8_t* par
 
 int b2g16_prove_batch(b2g16_ctx* hctx, const b2g16_pk* pk, const uint8_t* assignments32, size_t n_partitions,
                       const uint8_t* r32s, const uint8_t* s32s, int priority, uint8_t* proofs_out) {
-    (void)priority;
     Ctx* c = reinterpret_cast<Ctx*>(hctx);
     if (!c || !pk || (n_partitions && (!assignments32 || !r32s || !s32s || !proofs_out))) return B2G16_E_INVALID_ARG;
-    return guard(c, [&] {
-        const size_t zb = pk->n_vars * 32;
-        DevBuf<uint8_t> dz[2] = {DevBuf<uint8_t>(zb, c->stream), DevBuf<uint8_t>(zb, c->stream)};
-        for (size_t k = 0; k < n_partitions; ++k) {
-            B2_CUDA(cudaMemcpyAsync(dz[k & 1].get(), assignments32 + k * zb, zb, cudaMemcpyHostToDevice, c->stream));
-            prove_one(c, pk, dz[k & 1].get(), r32s + 32 * k, s32s + 32 * k, proofs_out + 192 * k, nullptr);
-        }
-    });
+    const size_t zb = pk->n_vars * 32;
+    // one admission per partition: a priority proof submitted from another thread (a PoSt proof while a sector's
+    // partitions are being proved, compound_proof.hpp:134) gets the device between two partitions of the batch
+    for (size_t k = 0; k < n_partitions; ++k) {
+        const int rc = guard(c, [&] {
+            DevBuf<uint8_t> dz(zb, c->stream);
+            B2_CUDA(cudaMemcpyAsync(dz.get(), assignments32 + k * zb, zb, cudaMemcpyHostToDevice, c->stream));
+            prove_one(c, pk, dz.get(), r32s + 32 * k, s32s + 32 * k, proofs_out + 192 * k, nullptr);
+        }, priority != 0);
+        if (rc != B2G16_OK) return rc;
+    }
+    return B2G16_OK;
 }
 
 int b2g16_synth_witness(b2g16_ctx* hctx, const b2g16_pk* pk, uint8_t* d_assignment32, uint64_t n_free) {

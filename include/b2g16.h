@@ -176,7 +176,9 @@ typedef struct {
  * compound_proof::circuit_proofs (S/core/proof/compound_proof.hpp:127-137) on behalf of
  * seal_commit_phase2 (F/api/seal.hpp:298-301) and generate_{window,winning}_post
  * (F/api/post.hpp:225,345).  assignment32 = (1, inputs, aux) = 1+n_in+n_aux scalars.
- * r, s are explicit (bit-exact parity); priority mirrors compound_proof.hpp:134. */
+ * r, s are explicit (bit-exact parity).  priority mirrors compound_proof.hpp:134: a context runs one call at a
+ * time, and a waiting call with priority != 0 is admitted before every waiting call without it (b2g16_prove_batch asks
+ * for admission once per partition, so a priority proof from another thread runs between two partitions of a batch). */
 int b2g16_prove(b2g16_ctx*, const b2g16_pk*, const uint8_t* assignment32, const uint8_t r32[32],
                 const uint8_t s32[32], int priority, uint8_t proof_out[192], b2g16_trace* trace);
 /* assignment already on the device; proof written to host */

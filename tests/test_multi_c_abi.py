@@ -63,3 +63,43 @@ def test_prove_batch_multi_equals_single_device(oracle, slots, n_part):
     assert e.value.code == -2 and "device" in str(e.value)
     m.key_free(k)
     m.close()
+
+
+@pytest.mark.gpu
+def test_priority_proof_runs_between_partitions_of_a_batch(oracle):
+    """compound_proof.hpp:134 `priority`: a PoSt proof submitted while a sector's partitions are being proved is admitted
+    ahead of the batch's remaining partitions (one admission per partition), and both results are still bit-exact."""
+    import threading
+    import time
+    import torch
+    from b2g16 import codec
+    log_m, n_in, n_free, seed, n_part = 16, 3, 8, 5, 6
+    toxic, r, sr = util.toxic_from_seed(seed)
+    ctx = lib.Context(0)
+    pk = ctx.pk_generate_synth(log_m, n_in, n_free, seed, toxic)
+    nv = pk.shape()["n_vars"]
+    dz = torch.zeros((nv, 32), dtype=torch.uint8, device="cuda:0")
+    head = codec.random_fr(1 + n_in + n_free, np.random.Generator(np.random.PCG64(seed))); head[0] = 0; head[0, 0] = 1
+    dz[: head.shape[0]] = torch.from_numpy(head).cuda()
+    ctx.synth_witness(pk, dz.data_ptr(), n_free)
+    z = dz.cpu().numpy()
+    want = ctx.prove(pk, z, r, sr)
+    zs = np.stack([z] * n_part); rs = np.stack([r] * n_part); ss = np.stack([sr] * n_part)
+    t = {}
+
+    def batch():
+        t["batch0"] = time.perf_counter()
+        t["batch"] = ctx.prove_batch(pk, zs, rs, ss)
+        t["batch1"] = time.perf_counter()
+
+    th = threading.Thread(target=batch)
+    th.start()
+    while "batch0" not in t:
+        time.sleep(0.0005)
+    time.sleep(0.01)                                   # the batch is inside its first partitions
+    got = ctx.prove(pk, z, r, sr, priority=True)
+    t["hi1"] = time.perf_counter()
+    th.join()
+    assert got == want and t["batch"] == want * n_part
+    assert t["hi1"] < t["batch1"], "the priority proof waited for the whole batch"
+    pk.free(); ctx.close()
