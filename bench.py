@@ -634,6 +634,8 @@ def big_proofs(ctx, torch, dist, dev, workload, rank, world, barrier, max_over_r
     Every proof is checked by the native verifier; sharded proofs must equal the single-GPU bytes."""
     from b2g16 import codec, shapes
     log_m, n_in, n_free, seed = WORKLOADS[workload][0], n_in_of(workload), BENCH_N_FREE, 2027
+    torch.cuda.synchronize()
+    torch.cuda.empty_cache()          # blocks torch's allocator still caches from the earlier legs are invisible to the library's pool
     toxic, r, sr = toxic_from_seed(seed)
     t0 = time.perf_counter()
     pk, vk = ctx.pk_generate_synth(log_m, n_in, n_free, seed, toxic, want_vk=True)

@@ -668,6 +668,7 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
         Xyzz<F>* head = pieces.get(); Xyzz<F>* tail = pieces.get() + n_chunks;
         uint32_t* hb = piece_bucket.get(); uint32_t* tb = piece_bucket.get() + n_chunks;
         if (kl.e0) B2_CUDA(cudaEventRecord(kl.e0, st));
+        bool tree_fell_back = false;
         if (tree_levels > 0) {
             // ---- affine tree levels, then the XYZZ accumulate over what is left; windows in groups that fit the memory
             const uint32_t K = ctx->tree_k, K2 = ctx->tree_k2;
@@ -686,24 +687,54 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
             B2_CUDA(cudaDeviceGetDefaultMemPool(&pool, ctx->device));
             B2_CUDA(cudaMemPoolGetAttribute(pool, cudaMemPoolAttrReservedMemCurrent, &reserved));
             B2_CUDA(cudaMemPoolGetAttribute(pool, cudaMemPoolAttrUsedMemCurrent, &used));
-            const size_t avail = (size_t)((free_b + (reserved - used)) * 0.85);
+            // 75 % of what the device and the pool's cache can still give (the rest is left to the transforms and multiexps
+            // of the same proof that allocate after this point on other streams); if the allocation fails all the same --
+            // a fragmented pool, another process on the device -- halve the window group and try again, and in the end run
+            // the whole accumulation on the XYZZ kernel, which needs no scratch of its own
+            const size_t avail = (size_t)((free_b + (reserved - used)) * 0.75);
             int wg = W;
             while (wg > 1 && group_bytes(wg) > avail) wg = (wg + 1) / 2;
             if (ctx->tree_wgroup > 0 && ctx->tree_wgroup < wg) wg = ctx->tree_wgroup;
-            const uint32_t nbg_max = (uint32_t)wg * B;
-            size_t cap[16]; caps(n * (size_t)wg, nbg_max, cap);
-            DevBuf<Affine<F>> ptsA(cap[0], st), ptsB(tree_levels > 1 ? cap[1] : 0, st);
-            DevBuf<F> pp0(cap[0], st);
-            DevBuf<uint32_t> offA((size_t)nbg_max + 1, st), offB((size_t)nbg_max + 1, st);
-            // product tree over the thread totals: depth d holds count_at(cap0, d) values
+            size_t cap[16];
+            DevBuf<Affine<F>> ptsA, ptsB;
+            DevBuf<F> pp0, top_scratch;
+            DevBuf<uint32_t> offA, offB;
+            std::vector<DevBuf<F>> val, ppd;
             int depth_top = 1;
-            while (tree_count_at((uint32_t)cap[0], depth_top, K, K2) > TREE_TOP) ++depth_top;
-            std::vector<DevBuf<F>> val(depth_top + 1), ppd(depth_top + 1);
-            for (int d = 1; d <= depth_top; ++d) {
-                val[d].alloc(tree_count_at((uint32_t)cap[0], d, K, K2) + 1, st);
-                if (d < depth_top) ppd[d].alloc(tree_count_at((uint32_t)cap[0], d, K, K2) + 1, st);
+            auto try_alloc = [&](int g) -> bool {
+                const uint32_t nbg_max = (uint32_t)g * B;
+                caps(n * (size_t)g, nbg_max, cap);
+                depth_top = 1;                                   // product tree over the thread totals: depth d holds count_at(cap0, d) values
+                while (tree_count_at((uint32_t)cap[0], depth_top, K, K2) > TREE_TOP) ++depth_top;
+                try {
+                    ptsA.alloc(cap[0], st); ptsB.alloc(tree_levels > 1 ? cap[1] : 0, st);
+                    pp0.alloc(cap[0], st);
+                    offA.alloc((size_t)nbg_max + 1, st); offB.alloc((size_t)nbg_max + 1, st);
+                    val.clear(); ppd.clear();
+                    val.resize(depth_top + 1); ppd.resize(depth_top + 1);
+                    for (int d = 1; d <= depth_top; ++d) {
+                        val[d].alloc(tree_count_at((uint32_t)cap[0], d, K, K2) + 1, st);
+                        if (d < depth_top) ppd[d].alloc(tree_count_at((uint32_t)cap[0], d, K, K2) + 1, st);
+                    }
+                    top_scratch.alloc(TREE_TOP, st);
+                    return true;
+                } catch (const CudaError& e) {
+                    if (e.e != cudaErrorMemoryAllocation) throw;
+                    cudaGetLastError();
+                    ptsA.free(); ptsB.free(); pp0.free(); offA.free(); offB.free(); val.clear(); ppd.clear(); top_scratch.free();
+                    return false;
+                }
+            };
+            bool have_scratch = try_alloc(wg);
+            while (!have_scratch && wg > 1) {
+                B2_CUDA(cudaMemPoolTrimTo(pool, 0));             // hand the pool's idle blocks back before the next attempt
+                wg = (wg + 1) / 2;
+                have_scratch = try_alloc(wg);
             }
-            DevBuf<F> top_scratch(TREE_TOP, st);
+            if (!have_scratch) {
+                tree_levels = 0;                                 // no room for even one window: plain XYZZ accumulation below
+                tree_fell_back = true;
+            } else {
             for (int w0 = 0; w0 < W; w0 += wg) {
                 const int w1 = w0 + wg < W ? w0 + wg : W;
                 const uint32_t nbg = (uint32_t)(w1 - w0) * B, b0 = (uint32_t)w0 * B;
@@ -746,9 +777,12 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
                 ctx->launches += 2;
             }
             if (kl.e1) B2_CUDA(cudaEventRecord(kl.e1, st));
-        } else {
+            }
+        }
+        if (tree_levels == 0) {
 #define B2_CH(THREADS, MINB) msm_accumulate_chunked_kernel<F, THREADS, MINB><<<148 * MINB, THREADS, 0, st>>>(d_bases, sorted.get(), off.get(), (uint32_t)nb, seg_acc.get(), head, tail, hb, tb)
         if (sizeof(F) > 48) B2_CH(64, 4);
+        else if (tree_fell_back) B2_CH(128, 2);              // the launch shape n_chunks was sized for
         else switch (ctx->acc_variant) {
             case 101: B2_CH(128, 1); break;
             case 102: B2_CH(128, 2); break;

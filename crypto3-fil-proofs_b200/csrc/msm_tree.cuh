@@ -82,18 +82,9 @@ template <class F> B2_HD Affine<F> tree_entry(const TreeIn<F>& in, uint32_t e) {
     }
     return tree_ld_affine(in.pts + e);
 }
-// L2 prefetch of entry e (first and last byte: a 96 / 192-byte point may straddle 128-byte lines).  The big level kernels
-// walk their outputs serially; without it every iteration starts with a DRAM-latency stall that two to four warps per
-// scheduler cannot cover (level 0 gathers random key points).
-template <class F> B2_HD void tree_prefetch_entry(const TreeIn<F>& in, uint32_t e, bool x_only) {
-#if defined(__CUDA_ARCH__)
-    const char* q = reinterpret_cast<const char*>(in.sorted ? in.bases + (in.sorted[e] & 0x7fffffffu) : in.pts + e);
-    asm volatile("prefetch.global.L2 [%0];" ::"l"(q));
-    asm volatile("prefetch.global.L2 [%0];" ::"l"(q + (x_only ? sizeof(F) : sizeof(Affine<F>)) - 4));
-#else
-    (void)in; (void)e; (void)x_only;
-#endif
-}
+// (An explicit prefetch.global.L2 of the next output's entries was measured and dropped: the prefix pass is DRAM-bound --
+// 62 % of peak in ncu -- and the addition pass multiplier-bound, so the extra requests only cost: G1 up0 3.9 -> 5.2 ms,
+// down0 13.8 -> 14.2 ms, G2 down0 50.5 -> 51.5 ms per 2^22 multiexp.)
 // x coordinate of entry e alone (the sign bit of a level-0 reference does not touch x)
 template <class F> B2_HD F tree_entry_x(const TreeIn<F>& in, uint32_t e) {
     if (in.sorted) return tree_ld_field(&in.bases[in.sorted[e] & 0x7fffffffu].x);
@@ -165,7 +156,6 @@ template <class F> B2_HD void tree_up0_body(const TreeIn<F>& in, const uint32_t*
         const uint32_t i0 = in.off[b] + 2 * (o - off_out[b]);
         const bool has_pair = i0 + 1 < in.off[b + 1];
         tree_st_field(pp + o, prod);
-        if (o + 1 < o_end && o + 1 < next && i0 + 3 < in.off[b + 1]) { tree_prefetch_entry(in, i0 + 2, true); tree_prefetch_entry(in, i0 + 3, true); }
         if (!has_pair) continue;
         // The denominator of an ordinary addition needs the two x coordinates only (half the bytes of the gather):
         // x != 0 rules out the identity, x0 != x1 the doubling / cancellation cases; everything else takes the full path.
@@ -230,7 +220,6 @@ template <class F> B2_HD void tree_down0_body(const TreeIn<F>& in, const uint32_
         while (o < first) { --b; first = off_out[b]; }
         const uint32_t i0 = in.off[b] + 2 * (o - first);
         const bool has_pair = i0 + 1 < in.off[b + 1];
-        if (o > (uint32_t)o0 && o > first) { tree_prefetch_entry(in, i0 - 2, false); tree_prefetch_entry(in, i0 - 1, false); }   // output o - 1, same bucket
         Affine<F> r;
         bool done = false;
         if (has_pair) {
