@@ -4,6 +4,7 @@
 // (un-vendored); called on behalf of compound_proof::circuit_proofs
 // (libs/storage/include/nil/filecoin/storage/proofs/core/proof/compound_proof.hpp:127-137).
 #include <cstdlib>
+#include <cuda.h>
 #include "common.cuh"
 #include "ntt_plan.cuh"
 
@@ -64,6 +65,7 @@ void ntt_init_roots(Ctx* c) {
     c->roots_inv = make_table(c, w.inv(), Fr::one(), 0, 1u << (NTT_ROOT_LOG - 1));
     const int smem = (int)(2 * sizeof(uint4) << NTT_TILE_LOG);
     B2_CUDA(cudaFuncSetAttribute(ntt_pass_kernel<256, 3, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+    B2_CUDA(cudaFuncSetAttribute(ntt_pass_kernel<256, 3, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     B2_CUDA(cudaFuncSetAttribute(ntt_pass_kernel<128, 3, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     B2_CUDA(cudaFuncSetAttribute(ntt_pass_kernel<256, 2, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     B2_CUDA(cudaFuncSetAttribute(ntt_pass_kernel<256, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
@@ -136,6 +138,26 @@ static NttTables tables(Ctx* c, const NttDomain* d, bool inverse) {
     return t;
 }
 
+// Tensor map of a vector of n Fr elements for the plane-wise tile load (ntt_kernels.cuh "TMA tile staging").  The encoder
+// is a driver entry point, fetched through the runtime so that the library does not link libcuda.
+static bool make_ntt_tmap(const Fr* src, uint64_t n, NttTmap* out) {
+    typedef CUresult (*EncodeFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*, const cuuint32_t*,
+                                 CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+    static EncodeFn encode = [] {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) != cudaSuccess || q != cudaDriverEntryPointSuccess) { cudaGetLastError(); fn = nullptr; }
+        return reinterpret_cast<EncodeFn>(fn);
+    }();
+    if (!encode) return false;
+    static_assert(sizeof(CUtensorMap) == sizeof(NttTmap), "tensor map size");
+    const cuuint64_t gdim[3] = {2, 2, n};                      // u64 words per half, halves per element, elements
+    const cuuint64_t gstride[2] = {16, 32};                    // bytes between halves, between elements
+    const cuuint32_t box[3] = {2, 1, 256}, estride[3] = {1, 1, 1};
+    return encode(reinterpret_cast<CUtensorMap*>(out), CU_TENSOR_MAP_DATA_TYPE_UINT64, 3, const_cast<Fr*>(src), gdim, gstride, box, estride,
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
+
 static void launch_pass(Ctx* c, const Fr* src, Fr* dst, const NttPass& p) {
     const uint64_t tiles = ntt_pass_tiles(p);
     const int T = 1 << (p.k + p.logc);
@@ -143,15 +165,19 @@ static void launch_pass(Ctx* c, const Fr* src, Fr* dst, const NttPass& p) {
     const int max_grid = 148 * 3 * 4;                      // 3 resident CTAs per SM, a few waves
     int grid = (int)(tiles < (uint64_t)max_grid ? tiles : (uint64_t)max_grid);
     static const int variant = getenv("B2G16_NTT_VARIANT") ? atoi(getenv("B2G16_NTT_VARIANT")) : 0;
-    if (variant == 0) {
+    static const int use_tma = getenv("B2G16_NTT_TMA") ? atoi(getenv("B2G16_NTT_TMA")) : 0;
+    NttTmap tmap{};
+    if (variant == 0 && use_tma && ntt_pass_tma_ok(p) && make_ntt_tmap(src, 1ull << p.log_n, &tmap)) {
+        ntt_pass_kernel<256, 3, false, true><<<grid, 256, smem, c->stream>>>(src, dst, p, tmap);
+    } else if (variant == 0) {
         const int block = T / 2 < 256 ? (T / 2 < 32 ? 32 : T / 2) : 256;
-        ntt_pass_kernel<256, 3, false><<<grid, block, smem, c->stream>>>(src, dst, p);
+        ntt_pass_kernel<256, 3, false><<<grid, block, smem, c->stream>>>(src, dst, p, tmap);
     } else {
         const int cap = variant == 1 ? 128 : 256;
         const int block = T / 8 < cap ? (T / 8 < 32 ? 32 : T / 8) : cap;     // one register-round slot = 8 elements
-        if (variant == 1) ntt_pass_kernel<128, 3, true><<<grid, block, smem, c->stream>>>(src, dst, p);
-        else if (variant == 2) ntt_pass_kernel<256, 2, true><<<grid, block, smem, c->stream>>>(src, dst, p);
-        else ntt_pass_kernel<256, 1, true><<<grid, block, smem, c->stream>>>(src, dst, p);
+        if (variant == 1) ntt_pass_kernel<128, 3, true><<<grid, block, smem, c->stream>>>(src, dst, p, tmap);
+        else if (variant == 2) ntt_pass_kernel<256, 2, true><<<grid, block, smem, c->stream>>>(src, dst, p, tmap);
+        else ntt_pass_kernel<256, 1, true><<<grid, block, smem, c->stream>>>(src, dst, p, tmap);
     }
     c->launches++;
     B2_CUDA(cudaGetLastError());

@@ -310,19 +310,66 @@ B2_HD void ntt_phase_store(const NttPass& p, const NttTile& t, Fr* data, const u
 }
 
 #if defined(__CUDACC__)
+// ---- TMA tile staging (cp.async.bulk.tensor + mbarrier) for plain loads of contiguous tiles ------------------
+// A contiguous pass reads its 2048-element tile from 64 KB of consecutive global memory.  Seen as a rank-3 tensor of
+// u64 -- (2 words, 2 halves, N elements), strides 8 / 16 / 32 B -- a box of (2, 1, 256) is 256 element *halves*, 16 B
+// each, packed: exactly one quarter-plane of the tile's shared-memory layout, and SWIZZLE_128B (16-byte chunk index XOR
+// 128-byte line index, on the shared address) is exactly ntt_swz.  Sixteen boxes fill both planes; one elected thread
+// issues them against an mbarrier and every thread waits on its phase -- no address arithmetic, no LDG / STS, no
+// registers for data in flight.  Only loads with nothing fused into them qualify (ntt_pass_tma_ok).
+B2_D uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+B2_D void mbar_init(uint64_t* b, uint32_t count) { asm volatile("mbarrier.init.shared::cta.b64 [%1], %0;" ::"r"(count), "r"(smem_u32(b)) : "memory"); }
+B2_D void mbar_expect_tx(uint64_t* b, uint32_t bytes) { asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%1], %0;" ::"r"(bytes), "r"(smem_u32(b)) : "memory"); }
+B2_D bool mbar_try_wait(uint64_t* b, uint32_t parity) {
+    uint32_t ok;
+    asm volatile("{\n\t.reg .pred P1;\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n\tselp.u32 %0, 1, 0, P1;\n\t}" : "=r"(ok) : "r"(smem_u32(b)), "r"(parity) : "memory");
+    return ok != 0;
+}
+B2_D void tma_load_3d(void* smem_dst, const void* tmap, uint64_t* bar, int c0, int c1, int c2) {
+    asm volatile("cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];"
+                 ::"r"(smem_u32(smem_dst)), "l"(reinterpret_cast<uint64_t>(tmap)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2) : "memory");
+}
+struct alignas(64) NttTmap { unsigned char bytes[128]; };      // a CUtensorMap, opaque here (cuda.h is included by ntt.cu only)
+#endif
+inline bool ntt_pass_tma_ok(const NttPass& p) {
+    return p.contiguous && !p.dit && !p.in_canon && !p.check_canon && !p.fuse_abc && p.scale_mode != 1 && p.tw_mode != 2 && p.k + p.logc == NTT_TILE_LOG;
+}
+#if defined(__CUDACC__)
 // THREADS x MINB: CTA size and CTAs per SM the kernel is compiled for; ROUNDS: three stages at a time on eight values in
 // registers (ntt_phase_round) instead of one stage per barrier (ntt_phase_stage).  A 2048-element tile is 64 KB of shared
 // memory, so at most three CTAs fit an SM.  B2G16_NTT_VARIANT: 0 = one stage per barrier, 256 x 3 (24 warps per SM);
 // 1 / 2 / 3 = register rounds at 128 x 3 (168 registers), 256 x 2 (128 registers, spills), 256 x 1 (no spills, 8 warps).
-template <int THREADS, int MINB, bool ROUNDS> static __global__ void __launch_bounds__(THREADS, MINB) ntt_pass_kernel(const Fr* src, Fr* data, const NttPass p) {
-    extern __shared__ uint4 smem[];
+template <int THREADS, int MINB, bool ROUNDS, bool TMA = false> static __global__ void __launch_bounds__(THREADS, MINB)
+ntt_pass_kernel(const Fr* src, Fr* data, const NttPass p, const __grid_constant__ NttTmap tmap) {
+    extern __shared__ __align__(1024) uint4 smem[];
+    __shared__ __align__(8) uint64_t mbar;
     const int T = 1 << (p.k + p.logc);
     uint4* s_lo = smem;
     uint4* s_hi = smem + T;
+    uint32_t phase = 0;
+    if (TMA) {
+        if (threadIdx.x == 0) { mbar_init(&mbar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+        __syncthreads();
+    }
     for (uint64_t tile_id = blockIdx.x; tile_id < ((1ull << p.log_n) >> (p.k + p.logc)); tile_id += gridDim.x) {
         const NttTile t = ntt_make_tile(p, tile_id);
-        for (int e = threadIdx.x; e < T; e += blockDim.x) ntt_phase_load(p, t, src, s_lo, s_hi, e);
-        __syncthreads();
+        if (TMA) {
+            if (threadIdx.x == 0) {
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // the previous tile's generic-proxy accesses come first
+                mbar_expect_tx(&mbar, (uint32_t)(2 * sizeof(uint4)) << NTT_TILE_LOG);
+                const int e0 = (int)(tile_id << NTT_TILE_LOG);
+#pragma unroll
+                for (int h = 0; h < 2; ++h)
+#pragma unroll
+                    for (int q = 0; q < (1 << NTT_TILE_LOG) / 256; ++q) tma_load_3d((h ? s_hi : s_lo) + q * 256, &tmap, &mbar, 0, h, e0 + q * 256);
+            }
+            uint32_t spins = 0;
+            while (!mbar_try_wait(&mbar, phase)) { if (++spins > (1u << 26)) __trap(); }   // a lost transaction must not hang the device
+            phase ^= 1u;
+        } else {
+            for (int e = threadIdx.x; e < T; e += blockDim.x) ntt_phase_load(p, t, src, s_lo, s_hi, e);
+            __syncthreads();
+        }
         if (ROUNDS) {
             const int n_rounds = ntt_round_count(p);
             for (int r = 0; r < n_rounds; ++r) {
