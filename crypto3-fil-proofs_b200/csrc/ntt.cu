@@ -155,7 +155,7 @@ static bool make_ntt_tmap(const Fr* src, uint64_t n, NttTmap* out) {
     const cuuint64_t gstride[2] = {16, 32};                    // bytes between halves, between elements
     const cuuint32_t box[3] = {2, 1, 256}, estride[3] = {1, 1, 1};
     return encode(reinterpret_cast<CUtensorMap*>(out), CU_TENSOR_MAP_DATA_TYPE_UINT64, 3, const_cast<Fr*>(src), gdim, gstride, box, estride,
-                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+                  CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_NONE, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
 }
 
 static void launch_pass(Ctx* c, const Fr* src, Fr* dst, const NttPass& p) {
@@ -168,7 +168,9 @@ static void launch_pass(Ctx* c, const Fr* src, Fr* dst, const NttPass& p) {
     static const int use_tma = getenv("B2G16_NTT_TMA") ? atoi(getenv("B2G16_NTT_TMA")) : 0;
     NttTmap tmap{};
     if (variant == 0 && use_tma && ntt_pass_tma_ok(p) && make_ntt_tmap(src, 1ull << p.log_n, &tmap)) {
-        ntt_pass_kernel<256, 3, false, true><<<grid, 256, smem, c->stream>>>(src, dst, p, tmap);
+        NttPass q = p;
+        q.no_swz = 1;
+        ntt_pass_kernel<256, 3, false, true><<<grid, 256, smem, c->stream>>>(src, dst, q, tmap);
     } else if (variant == 0) {
         const int block = T / 2 < 256 ? (T / 2 < 32 ? 32 : T / 2) : 256;
         ntt_pass_kernel<256, 3, false><<<grid, block, smem, c->stream>>>(src, dst, p, tmap);

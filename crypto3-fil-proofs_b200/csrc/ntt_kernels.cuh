@@ -49,6 +49,8 @@ B2_HD uint64_t ntt_digit_index(const NttDigits& d, uint64_t pos) {
     return idx;
 }
 
+B2_HD int ntt_swz_raw(int e, bool on) { return on ? (e ^ ((e >> 3) & 7)) : e; }
+
 struct NttPass {
     int log_n, L, k, logc;      // block log-size, row bits, column bits of the tile
     int contiguous;             // 1: last pass (rows contiguous, columns = adjacent blocks)
@@ -76,7 +78,9 @@ struct NttPass {
     int fuse_abc;               // load computes (x * b[pos] - c[pos]) * zinv   (witness map)
     const Fr* src_b; const Fr* src_c; Fr zinv;
     int* bad;                   // device flag, set when an in_canon input is >= r (device build only)
+    int no_swz;                 // 1: tile slots are not swizzled (tiles loaded by TMA)
 };
+B2_HD int ntt_swz(int e, const NttPass& p) { return ntt_swz_raw(e, !p.no_swz && p.k + p.logc >= 6); }
 
 struct Fr2x { uint4 lo, hi; };
 B2_HD Fr fr_from_planes(const uint4& lo, const uint4& hi) {
@@ -105,8 +109,8 @@ B2_HD uint32_t bitrev_u32(uint32_t x, int bits) {
 // Shared-memory slot of tile element e.  The register rounds below read a tile with lane strides of 8 or 32 elements
 // (the rows a thread owns are contiguous in the last round), which would put a quarter-warp's 16-byte accesses on the same
 // banks; XOR-ing the low three index bits with the next three spreads those strides over all 32 banks and only permutes
-// elements inside 128-byte blocks, so unit-stride accesses stay conflict-free.  Tiles smaller than 64 elements are left alone.
-B2_HD int ntt_swz(int e, int tile_log) { return tile_log >= 6 ? (e ^ ((e >> 3) & 7)) : e; }
+// elements inside 128-byte blocks, so unit-stride accesses stay conflict-free.  Tiles smaller than 64 elements are left alone, and so are tiles that a
+// tensor map fills (NttPass::no_swz: the TMA swizzle modes want a box row as wide as their span, the plane rows are 16 B).
 
 // ---- tile geometry -------------------------------------------------------------
 // tile element e in [0, 2^(k+logc)):  (row, col) and its global position.
@@ -168,7 +172,7 @@ B2_HD void ntt_phase_load(const NttPass& p, const NttTile& t, const Fr* data, ui
     if (p.fuse_abc) x = (x * fr_load(p.src_b + g) - fr_load(p.src_c + g)) * p.zinv;
     if (p.scale_mode == 1) x = x * ntt_scale(p, g);
     if (p.tw_mode == 2 && row != 0) x = x * ntt_twiddle(p, t.col0 + col, (uint32_t)row);
-    const int dst = ntt_swz(p.dit ? t.elem((int)bitrev_u32((uint32_t)row, p.k), col) : e, p.k + p.logc);
+    const int dst = ntt_swz(p.dit ? t.elem((int)bitrev_u32((uint32_t)row, p.k), col) : e, p);
     fr_to_planes(x, s_lo[dst], s_hi[dst]);
 }
 // Twiddle of the butterfly (row j of the half-block, column col) in the stage with half-size h = 2^hs.
@@ -201,7 +205,7 @@ B2_HD void ntt_phase_stage(const NttPass& p, const NttTile& t, uint4* s_lo, uint
     int h = 1 << hs;
     int j = rb & (h - 1), grp = rb >> hs;
     int r0 = (grp << (hs + 1)) | j;
-    int e0 = ntt_swz(t.elem(r0, col), p.k + p.logc), e1 = ntt_swz(t.elem(r0 + h, col), p.k + p.logc);
+    int e0 = ntt_swz(t.elem(r0, col), p), e1 = ntt_swz(t.elem(r0 + h, col), p);
     Fr u = fr_from_planes(s_lo[e0], s_hi[e0]);
     Fr v = fr_from_planes(s_lo[e1], s_hi[e1]);
     Fr w; bool neg;
@@ -237,7 +241,7 @@ B2_HD void ntt_butterfly(bool dit, bool has_w, bool neg, const Fr& w, Fr& u, Fr&
 // and the index arithmetic is paid once per 2^R elements.
 template <int R, bool DIT> B2_HD void ntt_phase_round(const NttPass& p, const NttTile& t, uint4* s_lo, uint4* s_hi, int hmin, int slot) {
     constexpr int M = 1 << R;
-    const int hmax = hmin + R - 1, tile_log = p.k + p.logc;
+    const int hmax = hmin + R - 1;
     int col, low, high;
     if (t.contiguous) {
         low = slot & ((1 << hmin) - 1);
@@ -251,7 +255,7 @@ template <int R, bool DIT> B2_HD void ntt_phase_round(const NttPass& p, const Nt
     const int base = (high << (hmax + 1)) | low;
     Fr v[M];
 #pragma unroll
-    for (int m = 0; m < M; ++m) { const int e = ntt_swz(t.elem(base | (m << hmin), col), tile_log); v[m] = fr_from_planes(s_lo[e], s_hi[e]); }
+    for (int m = 0; m < M; ++m) { const int e = ntt_swz(t.elem(base | (m << hmin), col), p); v[m] = fr_from_planes(s_lo[e], s_hi[e]); }
     // all 2^R - 1 twiddles of the round first (the stage with half-size bit b has 2^b distinct ones: the row's bits below
     // b), so that their global-memory latencies overlap instead of queueing in front of each stage
     Fr w[M - 1 > 0 ? M - 1 : 1];
@@ -277,7 +281,7 @@ template <int R, bool DIT> B2_HD void ntt_phase_round(const NttPass& p, const Nt
         }
     }
 #pragma unroll
-    for (int m = 0; m < M; ++m) { const int e = ntt_swz(t.elem(base | (m << hmin), col), tile_log); fr_to_planes(v[m], s_lo[e], s_hi[e]); }
+    for (int m = 0; m < M; ++m) { const int e = ntt_swz(t.elem(base | (m << hmin), col), p); fr_to_planes(v[m], s_lo[e], s_hi[e]); }
 }
 // Rounds of a pass: the k stages in execution order, three at a time; the last round takes what is left.
 // Round r covers execution-order stages [3r, min(3r+3, k)): DIF -> half-size bits hmin = k - 3r - R, DIT -> hmin = 3r.
@@ -300,7 +304,7 @@ B2_HD void ntt_phase_round_any(const NttPass& p, const NttTile& t, uint4* s_lo, 
 B2_HD int ntt_stage_hs(const NttPass& p, int i) { return p.dit ? i : p.k - 1 - i; }
 B2_HD void ntt_phase_store(const NttPass& p, const NttTile& t, Fr* data, const uint4* s_lo, const uint4* s_hi, int e) {
     int row = t.row_of(e), col = t.col_of(e);          // output row k1 (natural order)
-    int src = ntt_swz(p.dit ? e : t.elem((int)bitrev_u32((uint32_t)row, p.k), col), p.k + p.logc);
+    int src = ntt_swz(p.dit ? e : t.elem((int)bitrev_u32((uint32_t)row, p.k), col), p);
     Fr x = fr_from_planes(s_lo[src], s_hi[src]);
     uint64_t g = t.gpos(row, col);
     if (p.tw_mode == 1 && row != 0) x = x * ntt_twiddle(p, t.col0 + col, (uint32_t)row);
@@ -313,8 +317,8 @@ B2_HD void ntt_phase_store(const NttPass& p, const NttTile& t, Fr* data, const u
 // ---- TMA tile staging (cp.async.bulk.tensor + mbarrier) for plain loads of contiguous tiles ------------------
 // A contiguous pass reads its 2048-element tile from 64 KB of consecutive global memory.  Seen as a rank-3 tensor of
 // u64 -- (2 words, 2 halves, N elements), strides 8 / 16 / 32 B -- a box of (2, 1, 256) is 256 element *halves*, 16 B
-// each, packed: exactly one quarter-plane of the tile's shared-memory layout, and SWIZZLE_128B (16-byte chunk index XOR
-// 128-byte line index, on the shared address) is exactly ntt_swz.  Sixteen boxes fill both planes; one elected thread
+// each, packed: exactly one eighth of a plane of the tile's shared-memory layout (the tensor map's swizzle modes fault
+// with 16-byte box rows -- tools/tma_probe.cu -- so a TMA-filled tile keeps plain slots, NttPass::no_swz).  Sixteen boxes fill both planes; one elected thread
 // issues them against an mbarrier and every thread waits on its phase -- no address arithmetic, no LDG / STS, no
 // registers for data in flight.  Only loads with nothing fused into them qualify (ntt_pass_tma_ok).
 B2_D uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }

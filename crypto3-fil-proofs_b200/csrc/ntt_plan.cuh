@@ -83,7 +83,7 @@ inline std::vector<NttPass> ntt_build_passes(const NttPlan& pl, bool rn, const N
         q.cscale = Fr::one();
         q.digits = pl.digits;
         q.in_canon = q.check_canon = q.out_canon = q.perm_store = q.fuse_abc = 0;
-        q.src_b = q.src_c = nullptr; q.zinv = Fr::one(); q.bad = nullptr;
+        q.src_b = q.src_c = nullptr; q.zinv = Fr::one(); q.bad = nullptr; q.no_swz = 0;
         out.push_back(q);
     }
     return out;
