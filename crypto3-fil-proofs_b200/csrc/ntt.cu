@@ -165,7 +165,7 @@ static void launch_pass(Ctx* c, const Fr* src, Fr* dst, const NttPass& p) {
     const int max_grid = 148 * 3 * 4;                      // 3 resident CTAs per SM, a few waves
     int grid = (int)(tiles < (uint64_t)max_grid ? tiles : (uint64_t)max_grid);
     static const int variant = getenv("B2G16_NTT_VARIANT") ? atoi(getenv("B2G16_NTT_VARIANT")) : 0;
-    static const int use_tma = getenv("B2G16_NTT_TMA") ? atoi(getenv("B2G16_NTT_TMA")) : 0;
+    static const int use_tma = getenv("B2G16_NTT_TMA") ? atoi(getenv("B2G16_NTT_TMA")) : 1;   // on by default; 0 = per-thread loads
     NttTmap tmap{};
     if (variant == 0 && use_tma && ntt_pass_tma_ok(p) && make_ntt_tmap(src, 1ull << p.log_n, &tmap)) {
         NttPass q = p;
