@@ -177,6 +177,23 @@ static void remainder_group(int g, int rem, int p, int* first, int* size) {
     *first = p * base + (p < extra ? p : extra);
 }
 
+// The schedule b2g16_prove_batch_multi follows, as data (host-only; lets the plan be checked without a device):
+// plan[3 p .. 3 p + 2] = { wave, first device slot, number of slots } of partition p.
+int b2g16_multi_schedule(int n_devices, size_t n_partitions, uint32_t* plan) {
+    if (n_devices <= 0 || (n_partitions && !plan)) return B2G16_E_INVALID_ARG;
+    const size_t waves = n_partitions / (size_t)n_devices;
+    const int rem = (int)(n_partitions % (size_t)n_devices);
+    for (size_t p = 0; p < n_partitions; ++p) {
+        if (p < waves * (size_t)n_devices) { plan[3 * p] = (uint32_t)(p / n_devices); plan[3 * p + 1] = (uint32_t)(p % n_devices); plan[3 * p + 2] = 1; }
+        else {
+            int first, size;
+            remainder_group(n_devices, rem, (int)(p - waves * (size_t)n_devices), &first, &size);
+            plan[3 * p] = (uint32_t)waves; plan[3 * p + 1] = (uint32_t)first; plan[3 * p + 2] = (uint32_t)size;
+        }
+    }
+    return B2G16_OK;
+}
+
 int b2g16_prove_batch_multi(b2g16_mctx* m, const b2g16_mpk* k, const uint8_t* assignments32, size_t n_partitions, const uint8_t* r32s,
                             const uint8_t* s32s, int priority, uint8_t* proofs_out) {
     if (!m || !k || k->pk.size() != m->ctx.size() || (n_partitions && (!assignments32 || !r32s || !s32s || !proofs_out))) return B2G16_E_INVALID_ARG;

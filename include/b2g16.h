@@ -230,6 +230,8 @@ b2g16_pk* b2g16_mpk_device_key(const b2g16_mpk*, int slot);
 int b2g16_mpk_free(b2g16_mctx*, b2g16_mpk*);
 int b2g16_prove_multi(b2g16_mctx*, const b2g16_mpk*, const uint8_t* assignment32, const uint8_t r32[32], const uint8_t s32[32], int priority,
                       uint8_t proof_out[192]);
+/* the plan of b2g16_prove_batch_multi as data: plan[3 p ..] = { wave, first device slot, slots } of partition p (host-only) */
+int b2g16_multi_schedule(int n_devices, size_t n_partitions, uint32_t* plan);
 int b2g16_prove_batch_multi(b2g16_mctx*, const b2g16_mpk*, const uint8_t* assignments32, size_t n_partitions, const uint8_t* r32s,
                             const uint8_t* s32s, int priority, uint8_t* proofs_out);
 

@@ -23,6 +23,32 @@ def test_init_multi_without_a_device_is_an_error():
     assert e.value.code == -1
 
 
+@pytest.mark.parametrize("g,parts", [(8, 10), (8, 8), (8, 3), (4, 6), (3, 4), (2, 5), (1, 3), (8, 1), (5, 0)])
+def test_schedule_covers_every_device_once_per_wave(g, parts):
+    """b2g16_multi_schedule (host-only): full waves put partition p on device p mod g; the last partial wave splits ALL g
+    devices into one contiguous group per remaining partition, sizes differing by at most one -- the 8 x 1 + 2 x 4 plan
+    for the 10 partitions of a 32 GiB sector on 8 GPUs (constants.hpp:70-73)."""
+    import ctypes as C
+    plan = (C.c_uint32 * (3 * max(parts, 1)))()
+    assert lib.load().b2g16_multi_schedule(g, C.c_size_t(parts), plan) == 0
+    rows = [tuple(plan[3 * p:3 * p + 3]) for p in range(parts)]
+    waves = parts // g
+    for p in range(waves * g):
+        assert rows[p] == (p // g, p % g, 1)
+    rem = rows[waves * g:]
+    if rem:
+        assert all(w == waves for w, _, _ in rem)
+        cover = []
+        for _, first, size in rem:
+            cover += list(range(first, first + size))
+        assert cover == list(range(g))                                   # every device used exactly once, in order
+        sizes = [size for _, _, size in rem]
+        assert max(sizes) - min(sizes) <= 1 and sizes == sorted(sizes, reverse=True)
+    if (g, parts) == (8, 10):
+        assert rows[8] == (1, 0, 4) and rows[9] == (1, 4, 4)
+    assert lib.load().b2g16_multi_schedule(0, C.c_size_t(1), plan) == -1
+
+
 @pytest.mark.gpu
 @pytest.mark.parametrize("slots,n_part", [(2, 5), (3, 4), (4, 2), (1, 2)])
 def test_prove_batch_multi_equals_single_device(oracle, slots, n_part):
