@@ -21,6 +21,7 @@
 #include <random>
 #include <stdexcept>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 #include "../../b2g16.h"
@@ -59,6 +60,55 @@ template <std::size_t N> struct bytes_value {
     static bytes_value zero() { return bytes_value(); }
 };
 
+
+// Value arithmetic on the byte-encoded types, so that caller code written against crypto3's value types (P + Q, -P,
+// k * P on g1_type<>::value_type / g2_type<>::value_type; a + b, a * b, a.inversed() on scalar values) compiles and
+// gives canonical results.  Each operator is one library call on the device: meant for the O(1) glue arithmetic
+// around a proof (multi_proof bookkeeping, test assertions), not for loops -- those are what multiexp is for.
+namespace detail {
+inline bytes_value<32> fr_op(int op, const bytes_value<32>& a, const bytes_value<32>* b) {
+    bytes_value<32> r;
+    context& c = context::instance();
+    c.check(b2g16_field_op(c.get(), 0, op, a.data.data(), b ? b->data.data() : nullptr, 1, r.data.data()));
+    return r;
+}
+// p - y on 48 little-endian bytes (y != 0, y < p)
+inline void fq_negate(std::uint8_t* y) {
+    static const std::uint8_t P[48] = {0xab, 0xaa, 0xff, 0xff, 0xff, 0xff, 0xfe, 0xb9, 0xff, 0xff, 0x53, 0xb1, 0xfe, 0xff, 0xab, 0x1e,
+                                       0x24, 0xf6, 0xb0, 0xf6, 0xa0, 0xd2, 0x30, 0x67, 0xbf, 0x12, 0x85, 0xf3, 0x84, 0x4b, 0x77, 0x64,
+                                       0xd7, 0xac, 0x4b, 0x43, 0xb6, 0xa7, 0x1b, 0x4b, 0x9a, 0xe6, 0x7f, 0x39, 0xea, 0x11, 0x01, 0x1a};
+    bool zero = true;
+    for (int i = 0; i < 48; ++i) zero = zero && y[i] == 0;
+    if (zero) return;
+    int borrow = 0;
+    for (int i = 0; i < 48; ++i) { int v = (int)P[i] - (int)y[i] - borrow; borrow = v < 0; y[i] = (std::uint8_t)(v + (borrow << 8)); }
+}
+}  // namespace detail
+inline bytes_value<32> operator+(const bytes_value<32>& a, const bytes_value<32>& b) { return detail::fr_op(0, a, &b); }
+inline bytes_value<32> operator-(const bytes_value<32>& a, const bytes_value<32>& b) { return detail::fr_op(1, a, &b); }
+inline bytes_value<32> operator*(const bytes_value<32>& a, const bytes_value<32>& b) { return detail::fr_op(2, a, &b); }
+inline bytes_value<32> operator-(const bytes_value<32>& a) { return detail::fr_op(5, a, &a); }
+inline bytes_value<32> inversed(const bytes_value<32>& a) { return detail::fr_op(3, a, &a); }
+template <std::size_t N> typename std::enable_if<N == 96 || N == 192, bytes_value<N>>::type operator+(const bytes_value<N>& a, const bytes_value<N>& b) {
+    std::uint8_t two[2 * N];
+    std::memcpy(two, a.data.data(), N); std::memcpy(two + N, b.data.data(), N);
+    bytes_value<N> r;
+    context& c = context::instance();
+    c.check(N == 96 ? b2g16_g1_sum(c.get(), two, 2, r.data.data()) : b2g16_g2_sum(c.get(), two, 2, r.data.data()));
+    return r;
+}
+template <std::size_t N> typename std::enable_if<N == 96 || N == 192, bytes_value<N>>::type operator-(const bytes_value<N>& a) {
+    bytes_value<N> r = a;                                   // (x, -y); the identity (all zero) stays the identity
+    for (std::size_t o = N / 2; o < N; o += 48) detail::fq_negate(r.data.data() + o);
+    return r;
+}
+template <std::size_t N> typename std::enable_if<N == 96 || N == 192, bytes_value<N>>::type operator-(const bytes_value<N>& a, const bytes_value<N>& b) { return a + (-b); }
+template <std::size_t N> typename std::enable_if<N == 96 || N == 192, bytes_value<N>>::type operator*(const bytes_value<32>& k, const bytes_value<N>& p) {
+    bytes_value<N> r;
+    context& c = context::instance();
+    c.check(N == 96 ? b2g16_msm_g1(c.get(), p.data.data(), k.data.data(), 1, r.data.data()) : b2g16_msm_g2(c.get(), p.data.data(), k.data.data(), 1, r.data.data()));
+    return r;
+}
 
 // Cache entry names of S/core/parameter_cache.hpp:50-94,166-173 (v28-<prefix>-<sha256>.{params,vk,meta} under
 // $FIL_PROOFS_PARAMETER_CACHE) and the metadata file (:108-123).

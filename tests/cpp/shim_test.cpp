@@ -47,6 +47,15 @@ int main(int argc, char** argv) {
         bool threw = false;
         try { algebra::multiexp(b1.begin(), b1.end(), s.begin(), s.begin() + 1, 1); } catch (const b2g16::error&) { threw = true; }
         expect(threw, "length mismatch is rejected");
+        // value arithmetic on the point / scalar types (group law through the library): P + Q, k * P, -P, scalar field ops
+        fr one{}; one.data[0] = 1;
+        fr two = one + one, three = two + one;
+        std::vector<g1> pq = {b1[0], b1[1]}; std::vector<fr> k11 = {one, one}, k23 = {two, three};
+        expect(b1[0] + b1[1] == algebra::multiexp(pq.begin(), pq.end(), k11.begin(), k11.end()), "P + Q on g1 values");
+        expect(two * b1[0] + three * b1[1] == algebra::multiexp(pq.begin(), pq.end(), k23.begin(), k23.end()), "k * P on g1 values");
+        expect((b1[0] + (-b1[0])).is_zero() && b1[0] - b1[1] + b1[1] == b1[0], "-P and P - Q on g1 values");
+        expect(b2[0] + b2[0] == two * b2[0] && (b2[0] - b2[0]).is_zero(), "P + P, k * P, P - P on g2 values");
+        expect(three * inversed(three) == one && two - three + one == fr{} && -one + one == fr{}, "scalar field operators");
     }
     {   // evaluation_domain (a13)
         auto x = load<fr>("ntt_in");
