@@ -285,6 +285,19 @@ msm_fix_pieces_kernel(Xyzz<F>* __restrict__ bucket_acc, const Xyzz<F>* __restric
         const uint32_t b = tail_bucket[t];
         if (b == NO_BUCKET) continue;                    // warp-uniform
         Xyzz<F> acc = Xyzz<F>::identity();
+        {   // the usual case -- a bucket cut once or twice -- needs one or two additions, not a 32-lane tree of six
+            const bool mine0 = t + 1 + lane < n_chunks && head_bucket[t + 1 + lane] == b;
+            const uint32_t mask = __ballot_sync(0xffffffffu, mine0);
+            const int m = mask == 0xffffffffu ? 32 : __ffs((int)~mask) - 1;      // continuation pieces are contiguous from chunk t + 1
+            if (m <= 3) {
+                if (lane == 0) {
+                    acc = tail_part[t];
+                    for (int j = 0; j < m; ++j) { Xyzz<F> q = head_part[t + 1 + j]; xyzz_add_call(&acc, &q); }
+                    bucket_acc[b] = acc;
+                }
+                continue;
+            }
+        }
         if (lane == 0) acc = tail_part[t];
         // continuation pieces are contiguous chunks t+1, t+2, .. carrying the same bucket id
         for (uint32_t u = t + 1 + lane; ; u += 32) {

@@ -10,6 +10,7 @@
 //           -> 192-byte compressed proof (F/constants.hpp:93 SINGLE_PARTITION_PROOF_LEN)
 // The key layout mirrors scheme_params (S/core/crypto/scheme_params.hpp:38-67), dense.
 #include <cstring>
+#include <future>
 #include <thread>
 #include <vector>
 #include "msm_impl.cuh"
@@ -277,7 +278,12 @@ template <class HF, class DX> static b2h::Aff<HF> host_horner(const DX* win, int
 
 // abc_host: optional {a32, b32, c32} host evaluations supplied by the caller's synthesis (b2g16_prove_abc);
 // otherwise a, b, c come from the key's CSR matrices.
-static void assemble_proof(const b2g16_pk* pk, const MsmOut& out, const uint8_t* r32, const uint8_t* s32, uint8_t* proof_out, b2g16_trace* tr);
+// the blinding terms of a proof depend on (key, r, s) only: r delta_1, s delta_1, r s delta_1, s delta_2 -- four of the six
+// host scalar multiplications of the assembly, computed on a host thread while the device works
+struct BlindTerms { b2h::Pt<b2h::Fq> r_d1, s_d1, rs_d1; b2h::Pt<b2h::Fq2> s_d2; };
+static BlindTerms blind_terms(const b2g16_pk* pk, const uint8_t* r32, const uint8_t* s32);
+static void assemble_proof(const b2g16_pk* pk, const MsmOut& out, const uint8_t* r32, const uint8_t* s32, uint8_t* proof_out, b2g16_trace* tr,
+                           const BlindTerms* pre = nullptr);
 
 // part / parts: this call reduces only the contiguous slice [part n / parts, (part+1) n / parts) of each of the
 // five queries (one proof spread over several GPUs, b2g16_prove_partial); partial_out then receives the five
@@ -286,10 +292,12 @@ static void prove_one(Ctx* c, const b2g16_pk* pk, const uint8_t* d_z_canon, cons
                       uint8_t* proof_out, b2g16_trace* tr, const uint8_t* const* abc_host = nullptr,
                       unsigned part = 0, unsigned parts = 1, MsmOut* partial_out = nullptr,
                       const uint8_t* d_h_slice = nullptr, uint64_t h_first = 0, uint64_t h_count = 0) {
+    std::future<BlindTerms> blind;
     if (!partial_out) {
         bool ok = true;
         host_fr_from_bytes(r32, &ok); host_fr_from_bytes(s32, &ok);
         B2_REQUIRE(ok, B2G16_E_NOT_CANONICAL, "r / s not canonical");
+        blind = std::async(std::launch::async, [pk, r32, s32] { return blind_terms(pk, r32, s32); });   // joined in assemble below (or by the future's destructor on unwind)
     }
     auto lo_of = [&](uint64_t n) { return (size_t)(n * part / parts); };
     auto cnt_of = [&](uint64_t n) { return (size_t)(n * (part + 1) / parts - n * part / parts); };
@@ -387,7 +395,8 @@ static void prove_one(Ctx* c, const b2g16_pk* pk, const uint8_t* d_z_canon, cons
         for (auto& t : th) t.join();
     }
     if (partial_out) { *partial_out = out; return; }
-    assemble_proof(pk, out, r32, s32, proof_out, tr);
+    const BlindTerms pre = blind.get();
+    assemble_proof(pk, out, r32, s32, proof_out, tr, &pre);
 }
 
 // host assembly from the five multiexp results
@@ -401,24 +410,33 @@ static b2h::G2 to_host(const G2Affine& p) {
 // The ten scalar multiplications and three inversions of the assembly run in the 64-bit host arithmetic of
 // host_bls.hpp (~0.1 us per Fq product; the limb-by-limb emulation of the device multiplier that the unit tests
 // use costs 0.6 us, which made this step 18 ms of every proof).
-static void assemble_proof(const b2g16_pk* pk, const MsmOut& out, const uint8_t* r32, const uint8_t* s32, uint8_t* proof_out, b2g16_trace* tr) {
+static BlindTerms blind_terms(const b2g16_pk* pk, const uint8_t* r32, const uint8_t* s32) {
     bool ok = true;
     const Fr r = host_fr_from_bytes(r32, &ok), s = host_fr_from_bytes(s32, &ok);
     B2_REQUIRE(ok, B2G16_E_NOT_CANONICAL, "r / s not canonical");
     uint8_t rs32[32];
     { uint32_t c[8]; (r * s).to_canonical(c); memcpy(rs32, c, 32); }
+    const b2h::G1 d1 = to_host(pk->delta_g1);
+    BlindTerms t;
+    t.r_d1 = b2h::scalar_mul(d1, r32); t.s_d1 = b2h::scalar_mul(d1, s32); t.rs_d1 = b2h::scalar_mul(d1, rs32);
+    t.s_d2 = b2h::scalar_mul(to_host(pk->delta_g2), s32);
+    return t;
+}
+static void assemble_proof(const b2g16_pk* pk, const MsmOut& out, const uint8_t* r32, const uint8_t* s32, uint8_t* proof_out, b2g16_trace* tr,
+                           const BlindTerms* pre) {
+    BlindTerms own;
+    if (!pre) { own = blind_terms(pk, r32, s32); pre = &own; }
     typedef b2h::Pt<b2h::Fq> P1;
     typedef b2h::Pt<b2h::Fq2> P2;
     b2h::G1 ha, hb1, hl, hh;
     b2h::G2 hb2;
     B2_REQUIRE(b2h::g1_from_abi(out.a, &ha) && b2h::g1_from_abi(out.b1, &hb1) && b2h::g1_from_abi(out.l, &hl) && b2h::g1_from_abi(out.h, &hh) &&
                b2h::g2_from_abi(out.b2, &hb2), B2G16_E_INTERNAL, "prove: multiexp result not canonical");
-    const b2h::G1 d1 = to_host(pk->delta_g1);
-    const P1 A = P1::from(ha).add(P1::from(to_host(pk->alpha_g1))).add(b2h::scalar_mul(d1, r32));
-    const P2 Bq = P2::from(hb2).add(P2::from(to_host(pk->beta_g2))).add(b2h::scalar_mul(to_host(pk->delta_g2), s32));
-    const P1 B1 = P1::from(hb1).add(P1::from(to_host(pk->beta_g1))).add(b2h::scalar_mul(d1, s32));
+    const P1 A = P1::from(ha).add(P1::from(to_host(pk->alpha_g1))).add(pre->r_d1);
+    const P2 Bq = P2::from(hb2).add(P2::from(to_host(pk->beta_g2))).add(pre->s_d2);
+    const P1 B1 = P1::from(hb1).add(P1::from(to_host(pk->beta_g1))).add(pre->s_d1);
     const b2h::G1 Aa = A.affine(), B1a = B1.affine();
-    const P1 Cc = P1::from(hh).add(P1::from(hl)).add(b2h::scalar_mul(Aa, s32)).add(b2h::scalar_mul(B1a, r32)).add(P1::from(b2h::scalar_mul(d1, rs32).affine().neg()));
+    const P1 Cc = P1::from(hh).add(P1::from(hl)).add(b2h::scalar_mul(Aa, s32)).add(b2h::scalar_mul(B1a, r32)).add(P1::from(pre->rs_d1.affine().neg()));
     const b2h::G1 Ca = Cc.affine();
     const b2h::G2 Ba = Bq.affine();
     b2h::g1_compress(Aa, proof_out); b2h::g2_compress(Ba, proof_out + 48); b2h::g1_compress(Ca, proof_out + 144);
