@@ -439,6 +439,11 @@ class Context:
         self._chk(load().b2g16_fr_dot_device(self.h, C.c_void_p(d_a_ptr), C.c_void_p(d_b_ptr), C.c_size_t(n), _p(out)))
         return out
 
+    def fr_dot_device_noalloc(self, d_a_ptr, d_b_ptr, n, d_out_ptr, d_status_ptr=None):
+        """b2g16_fr_dot_device_noalloc: result (32 B) and status (int) are written to DEVICE memory; asynchronous."""
+        self._chk(load().b2g16_fr_dot_device_noalloc(self.h, C.c_void_p(d_a_ptr), C.c_void_p(d_b_ptr), C.c_size_t(n), C.c_void_p(d_out_ptr),
+                                                     C.c_void_p(d_status_ptr) if d_status_ptr else None))
+
     def mad32_peak(self):
         v, ms = C.c_double(), C.c_double()
         self._chk(load().b2g16_measure_mad32_peak(self.h, C.byref(v), C.byref(ms)))

@@ -358,6 +358,20 @@ int b2g16_field_op(b2g16_ctx*, int field, int op, const uint8_t* a, const uint8_
  * identity sum_i s_i (k_i G) = (sum_i s_i k_i) G, a size-independent parity property checked at full size */
 int b2g16_fr_dot_device(b2g16_ctx*, const uint8_t* d_a32, const uint8_t* d_b32, size_t n, uint8_t out32[32]);
 
+/* ---- an entry point that allocates nothing.  NO COUNTERPART IN THE REFERENCE: added
+ *      for callers that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that
+ *      forbid allocation).  The no-allocation variant of b2g16_fr_dot_device: d_out32 (DEVICE memory, 32 bytes) =
+ *      sum_i a_i b_i mod r over n canonical scalars; d_status (device int, may be NULL) = 0, or B2G16_E_NOT_CANONICAL
+ *      when an operand was >= r.  Its scratch -- one 32-byte partial sum per 4096 elements and the bad-input flag --
+ *      is a file-scope device array of 256 + 32 * B2G16_NOALLOC_MAX_BLOCKS = 131,328 bytes that every GPU loading the
+ *      library holds until exit; n > B2G16_NOALLOC_MAX_N (2^24) is refused with B2G16_E_INVALID_ARG.  The call enqueues
+ *      a memset and two kernels on the context's stream and returns without synchronising; it calls no cudaMalloc /
+ *      cudaFree / cudaMallocAsync.  All calls on one device share the array (it keeps the last call's contents; what
+ *      must start at zero is cleared by each call): calls that overlap on the GPU race -- serialise them. */
+#define B2G16_NOALLOC_MAX_BLOCKS 4096
+#define B2G16_NOALLOC_MAX_N (4096ull * B2G16_NOALLOC_MAX_BLOCKS)
+int b2g16_fr_dot_device_noalloc(b2g16_ctx*, const uint8_t* d_a32, const uint8_t* d_b32, size_t n, uint8_t* d_out32, int* d_status);
+
 #ifdef __cplusplus
 }
 #endif
