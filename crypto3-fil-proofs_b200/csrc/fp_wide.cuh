@@ -181,6 +181,38 @@ template <bool KARATSUBA> B2_HD Fq fq_mul(const Fq& a, const Fq& b) {
     Fq r; redc_wide<FqParams>(r.v, t); return r;
 }
 
+// a^2 for a 12-limb value through its 6-limb halves: a^2 = aL^2 + 2 aL aH 2^192 + aH^2 2^384 -- three 6 x 6 products
+// (108 wide MADs instead of 144) and ~40 additions; no sign handling, unlike the Karatsuba product.
+B2_HD void sqr_wide_halves12(uint32_t* t, const uint32_t* a) {
+    constexpr int h = 6;
+    uint32_t p0[2 * h], p2[2 * h], pm[2 * h + 1];
+    mul_wide<h>(p0, a, a);
+    mul_wide<h>(p2, a + h, a + h);
+    mul_wide<h>(pm, a, a + h);
+    // pm <- 2 pm (13 limbs)
+    pm[2 * h] = pm[2 * h - 1] >> 31;
+#pragma unroll
+    for (int i = 2 * h - 1; i > 0; --i) pm[i] = (pm[i] << 1) | (pm[i - 1] >> 31);
+    pm[0] <<= 1;
+    // t = p0 + pm 2^(32 h) + p2 2^(64 h)
+#pragma unroll
+    for (int i = 0; i < h; ++i) t[i] = p0[i];
+    t[h] = ptx::add_cc(p0[h], pm[0]);
+#pragma unroll
+    for (int i = 1; i < h; ++i) t[h + i] = ptx::addc_cc(p0[h + i], pm[i]);
+#pragma unroll
+    for (int i = 0; i < h; ++i) t[2 * h + i] = ptx::addc_cc(p2[i], pm[h + i]);
+    t[3 * h] = ptx::addc_cc(p2[h], pm[2 * h]);
+#pragma unroll
+    for (int i = 1; i < h - 1; ++i) t[3 * h + i] = ptx::addc_cc(p2[h + i], 0);
+    t[4 * h - 1] = ptx::addc(p2[2 * h - 1], 0);
+}
+B2_HD Fq fq_sqr_halves(const Fq& a) {
+    uint32_t t[24];
+    sqr_wide_halves12(t, a.v);
+    Fq r; redc_wide<FqParams>(r.v, t); return r;
+}
+
 // ---- Fq2 = Fq[u] / (u^2 + 1) with lazy reduction -------------------------------------------------
 // t -= s over 24 limbs; returns the borrow mask
 B2_HD uint32_t sub_wide(uint32_t* t, const uint32_t* s) { return sub_n<24>(t, t, s); }

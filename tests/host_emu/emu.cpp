@@ -50,7 +50,7 @@ int emu_g2_sum(int mode, const uint8_t* p, size_t n, uint8_t* out) { return sum_
 // fp_wide.cuh: which = 0 split product + reduction, 1 Karatsuba product + reduction (Fq, 48-byte canonical operands);
 // which = 2 / 3: Fq2 product with lazy reduction, schoolbook / Karatsuba (96-byte operands c0 || c1).  -1 on a non-canonical operand.
 int emu_wide_mul(int which, const uint8_t* a, const uint8_t* b, size_t n, uint8_t* out) {
-    const int comps = which >= 2 ? 2 : 1;
+    const int comps = (which == 2 || which == 3) ? 2 : 1;
     for (size_t i = 0; i < n; ++i) {
         Fq x[2], y[2];
         for (int k = 0; k < comps; ++k) {
@@ -60,7 +60,8 @@ int emu_wide_mul(int which, const uint8_t* a, const uint8_t* b, size_t n, uint8_
             x[k] = Fq::from_canonical(ca); y[k] = Fq::from_canonical(cb);
         }
         Fq r[2];
-        if (which == 0) r[0] = wide::fq_mul<false>(x[0], y[0]);
+        if (which == 4) r[0] = wide::fq_sqr_halves(x[0]);                     // b ignored
+        else if (which == 0) r[0] = wide::fq_mul<false>(x[0], y[0]);
         else if (which == 1) r[0] = wide::fq_mul<true>(x[0], y[0]);
         else {
             const Fq2 z = which == 2 ? wide::fq2_mul_lazy<false>(Fq2{x[0], x[1]}, Fq2{y[0], y[1]}) : wide::fq2_mul_lazy<true>(Fq2{x[0], x[1]}, Fq2{y[0], y[1]});

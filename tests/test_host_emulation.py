@@ -117,6 +117,9 @@ def test_wide_products_vs_oracle(emu, oracle):
         out = np.zeros_like(a)
         assert emu.emu_wide_mul(which, _p(a), _p(b), C.c_size_t(2 * n), _p(out)) == 0
         assert np.array_equal(out, want), which
+    out = np.zeros_like(a)                                                  # which = 4: squaring through the 6-limb halves
+    assert emu.emu_wide_mul(4, _p(a), _p(b), C.c_size_t(2 * n), _p(out)) == 0
+    assert np.array_equal(out, enc([x * x % P for x in ai]))
     w2 = []
     for k in range(n):
         a0, a1, b0, b1 = ai[2 * k], ai[2 * k + 1], bi[2 * k], bi[2 * k + 1]
