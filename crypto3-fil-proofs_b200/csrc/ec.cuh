@@ -84,6 +84,13 @@ template <class F> struct Xyzz {
         F I = (ZZ * ZZZ).inv();
         return {X * I * ZZZ, Y * I * ZZ};
     }
+    // the same point with the inversion by the binary Euclidean algorithm (fp.cuh inv_gcd): a much shorter serial chain
+    // than the Fermat ladder, which is what a lone thread at the end of a multiexp pays for
+    B2_HD Affine<F> to_affine_gcd() const {
+        if (is_identity()) return Affine<F>::identity();
+        F I = (ZZ * ZZZ).inv_gcd();
+        return {X * I * ZZZ, Y * I * ZZ};
+    }
 };
 
 #if defined(__CUDACC__)
