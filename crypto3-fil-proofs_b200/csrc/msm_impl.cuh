@@ -569,25 +569,14 @@ static void launch_accumulate_v(cudaStream_t st, size_t max_segs, const Affine<F
     constexpr int THREADS = sizeof(F) > 48 ? 64 : 128;
     msm_accumulate_kernel<F, THREADS, MINB, PF><<<grid_for(max_segs, THREADS, 148 * 64), THREADS, 0, st>>>(bases, sorted, hist, off, seg_off, nb, S, seg_acc);
 }
-// variant = 10 * min_blocks_per_SM + prefetch_mode (tuning knob B2G16_ACC_VARIANT; default below)
+// one thread per bucket segment (the path of G2 at <= 16-bit windows when the tree levels are switched off, and of
+// acc_variant < 100).  The prefetch / occupancy variants of round 1 (PF 1 / 2, 3-4 CTAs per SM) were measured slower
+// and are no longer instantiated.
 template <class F>
 static void launch_accumulate(Ctx* ctx, cudaStream_t st, size_t max_segs, const Affine<F>* bases, const uint32_t* sorted, const uint32_t* hist, const uint32_t* off,
                               const uint32_t* seg_off, uint32_t nb, uint32_t S, Xyzz<F>* seg_acc) {
     ctx->launches++;
-#define B2_ACC(MINB, PF) launch_accumulate_v<F, MINB, PF>(st, max_segs, bases, sorted, hist, off, seg_off, nb, S, seg_acc)
-    if (sizeof(F) > 48) { B2_ACC(1, 0); return; }
-    switch (ctx->acc_variant) {
-        case 10: B2_ACC(1, 0); break;
-        case 11: B2_ACC(1, 1); break;
-        case 12: B2_ACC(1, 2); break;
-        case 30: B2_ACC(3, 0); break;
-        case 31: B2_ACC(3, 1); break;
-        case 32: B2_ACC(3, 2); break;
-        case 40: B2_ACC(4, 0); break;
-        case 41: B2_ACC(4, 1); break;
-        default: B2_ACC(1, 0);
-    }
-#undef B2_ACC
+    launch_accumulate_v<F, 1, 0>(st, max_segs, bases, sorted, hist, off, seg_off, nb, S, seg_acc);
 }
 
 // d_win_out == nullptr: the affine result goes to d_out_bytes (Horner over the windows by one device thread).
@@ -628,16 +617,14 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
     if (tree_levels > 12) tree_levels = 12;
     // G2 at 16-bit windows: the one-thread-per-bucket kernel is faster (measured 86 vs 99 ms at 2^22)
     const bool chunked = (ctx->acc_variant >= 100 && !(sizeof(F) > 48 && c <= 16)) || tree_levels > 0;
-    // chunked-accumulate launch shape (threads per CTA, CTAs per SM).  G1 at 194 registers per thread: 2 x 160
-    // threads = 10 warps per SM is the most that fits the register file without spilling (variant 105);
-    // 101..104 = 128-thread CTAs, 1..4 per SM; 106 = 3 x 96.  G2: 64-thread CTAs at the 255-register cap, 4 per SM.
+    // chunked-accumulate launch shape (threads per CTA, CTAs per SM).  G1 at 194 registers per thread: 2 x 128 threads per
+    // SM (variant 102, the default); 101 / 103 = 1 / 3 CTAs per SM.  160- and 96-thread CTAs and 4 CTAs per SM were
+    // measured slower in round 1 and are gone.  G2: 64-thread CTAs at the 255-register cap, 4 per SM.
     int ch_threads = 0, ch_minb = 0;
     if (chunked) {
         if (sizeof(F) > 48) { ch_threads = 64; ch_minb = 4; }
         else if (ctx->acc_variant < 100 || tree_levels > 0) { ch_threads = 128; ch_minb = 2; }
-        else if (ctx->acc_variant == 105) { ch_threads = 160; ch_minb = 2; }
-        else if (ctx->acc_variant == 106) { ch_threads = 96; ch_minb = 3; }
-        else { ch_threads = 128; ch_minb = ctx->acc_variant - 100; }
+        else { ch_threads = 128; ch_minb = ctx->acc_variant == 101 ? 1 : ctx->acc_variant == 103 ? 3 : 2; }
     }
     const uint32_t n_chunks = chunked ? (uint32_t)(148 * ch_minb * ch_threads) : 0;
     DevBuf<uint32_t> hist(nb + 1, st), off(nb + 1, st), cursor(nb + 1, st), seg_off(chunked ? 0 : nb + 1, st), tile_sums((size_t)n_tiles + 1, st), sorted(max_entries, st);
@@ -802,12 +789,8 @@ void msm_run(Ctx* ctx, const Affine<F>* d_bases, const uint32_t* d_scalars, size
         else if (tree_fell_back) B2_CH(128, 2);              // the launch shape n_chunks was sized for
         else switch (ctx->acc_variant) {
             case 101: B2_CH(128, 1); break;
-            case 102: B2_CH(128, 2); break;
             case 103: B2_CH(128, 3); break;
-            case 104: B2_CH(128, 4); break;
-            case 105: B2_CH(160, 2); break;
-            case 106: B2_CH(96, 3); break;
-            default: B2_REQUIRE(false, B2G16_E_INVALID_ARG, "msm: chunked accumulate variant must be 101..106");
+            default: B2_CH(128, 2);                          // 102: two CTAs of 128 threads per SM (194 registers, no spills)
         }
 #undef B2_CH
         if (kl.e1) B2_CUDA(cudaEventRecord(kl.e1, st));
