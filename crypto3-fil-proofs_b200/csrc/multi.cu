@@ -5,8 +5,9 @@
 // circuits of a proof to one prover call, and seal_commit_phase2 / generate_window_post
 // (libs/filecoin/include/nil/filecoin/proofs/api/seal.hpp:298-308, api/post.hpp:305-348) write the proofs back in
 // partition order.  These entry points give that caller every GPU of the box without torch.distributed:
-//   * b2g16_prove_batch_multi: partitions -> devices.  Full waves run one partition per device (independent units, the
-//     key replicated, no data-path exchange); the last partial wave splits the devices into groups and each group
+//   * b2g16_prove_batch_multi: partitions -> devices.  Full waves run one partition per device at a time (independent
+//     units, the key replicated, no data-path exchange; device i takes a contiguous run of partitions through
+//     b2g16_prove_batch, which overlaps the next witness upload with the current proof); the last partial wave splits the devices into groups and each group
 //     proves ONE partition in latency mode (every member reduces its slice of the five queries,
 //     b2g16_prove_partial; 576 bytes per member come back to the host and are assembled), so no device idles.
 //   * b2g16_prove_multi: one proof over all devices in latency mode (a WindowPoSt / WinningPoSt proof is one partition).
@@ -184,7 +185,9 @@ int b2g16_multi_schedule(int n_devices, size_t n_partitions, uint32_t* plan) {
     const size_t waves = n_partitions / (size_t)n_devices;
     const int rem = (int)(n_partitions % (size_t)n_devices);
     for (size_t p = 0; p < n_partitions; ++p) {
-        if (p < waves * (size_t)n_devices) { plan[3 * p] = (uint32_t)(p / n_devices); plan[3 * p + 1] = (uint32_t)(p % n_devices); plan[3 * p + 2] = 1; }
+        // full waves: device i proves the contiguous run [i waves, (i + 1) waves) -- one b2g16_prove_batch per device, which
+        // uploads the next witness while the current partition is proved
+        if (p < waves * (size_t)n_devices) { plan[3 * p] = (uint32_t)(p % waves); plan[3 * p + 1] = (uint32_t)(p / waves); plan[3 * p + 2] = 1; }
         else {
             int first, size;
             remainder_group(n_devices, rem, (int)(p - waves * (size_t)n_devices), &first, &size);
@@ -204,10 +207,10 @@ int b2g16_prove_batch_multi(b2g16_mctx* m, const b2g16_mpk* k, const uint8_t* as
     const int rem = (int)(n_partitions % (size_t)g);
     std::vector<uint8_t> partials((size_t)g * 576);              // remainder wave: one slot per context
     int rc = fan_out(m, [&](int i) {
-        for (size_t w = 0; w < waves; ++w) {                        // full waves: partition w g + i on context i
-            const size_t p = w * (size_t)g + (size_t)i;
-            const int r = b2g16_prove(m->ctx[i], k->pk[i], assignments32 + p * zb, r32s + 32 * p, s32s + 32 * p, priority, proofs_out + 192 * p, nullptr);
-            if (r != B2G16_OK) { note_error(m, i, r, "b2g16_prove"); return r; }
+        if (waves) {                                                // full waves: partitions [i waves, (i + 1) waves) on context i
+            const size_t p = (size_t)i * waves;
+            const int r = b2g16_prove_batch(m->ctx[i], k->pk[i], assignments32 + p * zb, waves, r32s + 32 * p, s32s + 32 * p, priority, proofs_out + 192 * p);
+            if (r != B2G16_OK) { note_error(m, i, r, "b2g16_prove_batch"); return r; }
         }
         for (int q = 0; q < rem; ++q) {                             // remainder wave: context i is member (i - first) of one group
             int first, size;

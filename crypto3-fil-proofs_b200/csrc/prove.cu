@@ -723,15 +723,42 @@ int b2g16_prove_batch(b2g16_ctx* hctx, const b2g16_pk* pk, const uint8_t* assign
                       const uint8_t* r32s, const uint8_t* s32s, int priority, uint8_t* proofs_out) {
     Ctx* c = reinterpret_cast<Ctx*>(hctx);
     if (!c || !pk || (n_partitions && (!assignments32 || !r32s || !s32s || !proofs_out))) return B2G16_E_INVALID_ARG;
+    if (n_partitions == 0) return B2G16_OK;
     const size_t zb = pk->n_vars * 32;
+    // Two witness buffers and a copy stream of their own: partition k + 1 is uploaded by a helper thread while partition k
+    // is proved (a caller's witnesses are ordinary pageable memory, whose upload is a host-driven staged copy: 10-15 ms of
+    // a 150 ms proof at 2^22 when it sits in front of every proof).  The buffers are plain cudaMalloc memory, so the copy
+    // stream and the proving stream need no allocator hand-over; ordering is by the host (the upload is synchronised
+    // before the proof that reads it is launched, a proof is complete before its buffer is written again).
+    struct Bufs {
+        int device; uint8_t* dz[2] = {nullptr, nullptr}; cudaStream_t copy = nullptr;
+        ~Bufs() { cudaSetDevice(device); for (auto p : dz) if (p) cudaFree(p); if (copy) cudaStreamDestroy(copy); }
+    } bufs{c->device};
+    int rc = guard(c, [&] {
+        for (auto& p : bufs.dz) B2_CUDA(cudaMalloc((void**)&p, zb));
+        B2_CUDA(cudaStreamCreateWithFlags(&bufs.copy, cudaStreamNonBlocking));
+    }, priority != 0);
+    if (rc != B2G16_OK) return rc;
+    const int device = c->device;
+    auto upload = [&bufs, assignments32, zb, device](size_t k) -> cudaError_t {
+        cudaError_t e = cudaSetDevice(device);
+        if (e == cudaSuccess) e = cudaMemcpyAsync(bufs.dz[k & 1], assignments32 + k * zb, zb, cudaMemcpyHostToDevice, bufs.copy);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(bufs.copy);
+        return e;
+    };
+    cudaError_t up = upload(0);
     // one admission per partition: a priority proof submitted from another thread (a PoSt proof while a sector's
     // partitions are being proved, compound_proof.hpp:134) gets the device between two partitions of the batch
     for (size_t k = 0; k < n_partitions; ++k) {
-        const int rc = guard(c, [&] {
-            DevBuf<uint8_t> dz(zb, c->stream);
-            B2_CUDA(cudaMemcpyAsync(dz.get(), assignments32 + k * zb, zb, cudaMemcpyHostToDevice, c->stream));
-            prove_one(c, pk, dz.get(), r32s + 32 * k, s32s + 32 * k, proofs_out + 192 * k, nullptr);
-        }, priority != 0);
+        if (up != cudaSuccess) {
+            cudaGetLastError();
+            guard(c, [&] { throw CudaError{up, "witness upload (b2g16_prove_batch)", __FILE__, __LINE__}; });
+            return B2G16_E_CUDA;
+        }
+        std::future<cudaError_t> next;
+        if (k + 1 < n_partitions) next = std::async(std::launch::async, upload, k + 1);
+        rc = guard(c, [&] { prove_one(c, pk, bufs.dz[k & 1], r32s + 32 * k, s32s + 32 * k, proofs_out + 192 * k, nullptr); }, priority != 0);
+        if (next.valid()) up = next.get();                 // always joined, also when the proof failed
         if (rc != B2G16_OK) return rc;
     }
     return B2G16_OK;

@@ -178,7 +178,8 @@ typedef struct {
  * (F/api/post.hpp:225,345).  assignment32 = (1, inputs, aux) = 1+n_in+n_aux scalars.
  * r, s are explicit (bit-exact parity).  priority mirrors compound_proof.hpp:134: a context runs one call at a
  * time, and a waiting call with priority != 0 is admitted before every waiting call without it (b2g16_prove_batch asks
- * for admission once per partition, so a priority proof from another thread runs between two partitions of a batch). */
+ * for admission once per partition, so a priority proof from another thread runs between two partitions of a batch).
+ * b2g16_prove_batch uploads the witness of partition k + 1 on its own stream while partition k is proved. */
 int b2g16_prove(b2g16_ctx*, const b2g16_pk*, const uint8_t* assignment32, const uint8_t r32[32],
                 const uint8_t s32[32], int priority, uint8_t proof_out[192], b2g16_trace* trace);
 /* assignment already on the device; proof written to host */
@@ -210,7 +211,8 @@ int b2g16_prove_batch(b2g16_ctx*, const b2g16_pk*, const uint8_t* assignments32,
  *      127-137; F/api/seal.hpp:298-308, F/api/post.hpp:305-348): these entry points spread that call over the devices
  *      given to b2g16_init_multi, one context and one host thread per device, no torch.distributed and no NCCL (the only
  *      exchange is 576 bytes of partial sums per device and proof, which come back through the host).
- *   b2g16_prove_batch_multi: partition p of a full wave runs on device p mod n; the last, partial wave splits the devices
+ *   b2g16_prove_batch_multi: with w = n_partitions / n full waves, device i proves partitions [i w, (i + 1) w) one after
+ *      the other (b2g16_prove_batch: the next witness is uploaded while the current proof runs); the last, partial wave splits the devices
  *      into one group per remaining partition and every group proves its partition in latency mode.  Proofs are written
  *      in partition order; each equals what b2g16_prove returns for the same inputs.
  *   b2g16_prove_multi: one proof over all n devices in latency mode (b2g16_prove_partial on every device + assemble).

@@ -25,7 +25,7 @@ def test_init_multi_without_a_device_is_an_error():
 
 @pytest.mark.parametrize("g,parts", [(8, 10), (8, 8), (8, 3), (4, 6), (3, 4), (2, 5), (1, 3), (8, 1), (5, 0)])
 def test_schedule_covers_every_device_once_per_wave(g, parts):
-    """b2g16_multi_schedule (host-only): full waves put partition p on device p mod g; the last partial wave splits ALL g
+    """b2g16_multi_schedule (host-only): in the w full waves device i takes partitions [i w, (i + 1) w); the last partial wave splits ALL g
     devices into one contiguous group per remaining partition, sizes differing by at most one -- the 8 x 1 + 2 x 4 plan
     for the 10 partitions of a 32 GiB sector on 8 GPUs (constants.hpp:70-73)."""
     import ctypes as C
@@ -34,7 +34,7 @@ def test_schedule_covers_every_device_once_per_wave(g, parts):
     rows = [tuple(plan[3 * p:3 * p + 3]) for p in range(parts)]
     waves = parts // g
     for p in range(waves * g):
-        assert rows[p] == (p // g, p % g, 1)
+        assert rows[p] == (p % waves, p // waves, 1)                     # device i: the contiguous run [i w, (i + 1) w)
     rem = rows[waves * g:]
     if rem:
         assert all(w == waves for w, _, _ in rem)
