@@ -5,7 +5,7 @@
 // read path core/parameter_cache.hpp:125-129).  On a GPU the key must be resident, so the equivalent is:
 //   b2g16_params_map   : the offset / count table of the five queries and the vk block (what build_mapped_parameters
 //                        computes), from the length prefixes alone -- no point is read;
-//   b2g16_pk_load_file : streams each query through a ring of pinned host buffers (fread of chunk k+1 overlaps the
+//   b2g16_pk_load_file : streams each query through a ring of pinned host buffers (the read of chunk k+1 -- positioned reads split over four threads -- overlaps the
 //                        cudaMemcpyAsync + conversion kernel of chunk k) and converts ON THE DEVICE: big-endian file
 //                        coordinates -> little-endian limbs -> Montgomery form, range + curve checks, G2 coefficient
 //                        order, infinity flag.  Density-filtered a / b_g1 / b_g2 queries (bellman's layout) are expanded
@@ -141,8 +141,7 @@ bool read_parallel(FILE* f, uint64_t at, uint8_t* dst, size_t len) {
 template <bool G2> void stream_query(Ctx* c, FILE* f, uint64_t offset, uint64_t n, const uint32_t* d_pos, uint8_t* out_base, Ring& ring, int* d_bad, int& slot) {
     constexpr size_t SZ = G2 ? 192 : 96;
     const size_t per = ring.bytes / SZ;
-    B2_REQUIRE(fseeko(f, (off_t)offset, SEEK_SET) == 0, B2G16_E_INVALID_ARG, "parameter file: seek failed");
-    for (uint64_t f0 = 0; f0 < n; f0 += per) {
+    for (uint64_t f0 = 0; f0 < n; f0 += per) {                             // positioned reads (pread): the FILE's own offset is not used
         const size_t k = (size_t)(n - f0 < per ? n - f0 : per);
         B2_CUDA(cudaEventSynchronize(ring.done[slot]));                 // the slot's previous chunk has been consumed
         B2_REQUIRE(read_parallel(f, offset + f0 * SZ, ring.host[slot], k * SZ), B2G16_E_INVALID_ARG, "parameter file: short read");
@@ -233,13 +232,12 @@ int b2g16_pk_load_file(b2g16_ctx* hctx, const char* path, const b2g16_r1cs_view*
             const size_t chunk = (size_t)(c->key_chunk_mib > 0 ? c->key_chunk_mib : 32) << 20;
             Ring ring(chunk - chunk % 192);
             int slot = 0;
-            auto dense = [&](int q, const b2g16_csr& mat, uint64_t n_always, uint64_t width, const char* what, DevBuf<uint32_t>& d_pos) -> const uint32_t* {
+            auto dense = [&](int q, const b2g16_csr& mat, uint64_t n_always, const char* what, DevBuf<uint32_t>& d_pos) -> const uint32_t* {
                 if (ix.count[q] == nv) return nullptr;
                 std::vector<uint32_t> pos = dense_positions(mat, nv, n_always, ix.count[q], what);
                 d_pos.alloc(pos.size() + 1, c->stream);
                 B2_CUDA(cudaMemcpyAsync(d_pos.get(), pos.data(), pos.size() * sizeof(uint32_t), cudaMemcpyHostToDevice, c->stream));
                 B2_CUDA(cudaStreamSynchronize(c->stream));                // pos is a local
-                (void)width;
                 return d_pos.get();
             };
             B2_CUDA(cudaMalloc((void**)&pk->h, m * sizeof(G1Affine)));
@@ -249,11 +247,11 @@ int b2g16_pk_load_file(b2g16_ctx* hctx, const char* path, const b2g16_r1cs_view*
             DevBuf<uint32_t> pos_a, pos_b;
             B2_CUDA(cudaMalloc((void**)&pk->a, (nv + 1) * sizeof(G1Affine)));
             B2_CUDA(cudaMemsetAsync(pk->a, 0, nv * sizeof(G1Affine), c->stream));        // absent entries = identity
-            const uint32_t* pa = dense(3, cs->A, cs->n_in + 1, 96, "a query", pos_a);
+            const uint32_t* pa = dense(3, cs->A, cs->n_in + 1, "a query", pos_a);
             stream_query<false>(c, f, ix.offset[3], ix.count[3], pa, (uint8_t*)pk->a, ring, bad.ptr(), slot);
             B2_CUDA(cudaMalloc((void**)&pk->b_g1, (nv + 1) * sizeof(G1Affine)));
             B2_CUDA(cudaMemsetAsync(pk->b_g1, 0, nv * sizeof(G1Affine), c->stream));
-            const uint32_t* pb = dense(4, cs->B, 0, 96, "b_g1 query", pos_b);
+            const uint32_t* pb = dense(4, cs->B, 0, "b_g1 query", pos_b);
             stream_query<false>(c, f, ix.offset[4], ix.count[4], pb, (uint8_t*)pk->b_g1, ring, bad.ptr(), slot);
             B2_CUDA(cudaMalloc((void**)&pk->b_g2, (nv + 1) * sizeof(G2Affine)));
             B2_CUDA(cudaMemsetAsync(pk->b_g2, 0, nv * sizeof(G2Affine), c->stream));
