@@ -106,7 +106,36 @@ B2_HD Fq tree_sqr(const Fq& a) { return wide::fq_sqr_halves(a); }     // 108 + 1
 #else
 B2_HD Fq tree_sqr(const Fq& a) { return a.sqr(); }
 #endif
-#if B2_TREE_INLINE_FQ2
+// -DB2_TREE_FQ2_CALLS=1: the lazy product built from two out-of-line pieces (12 x 12 wide product, Montgomery reduction)
+// instead of fully inlined -- a ~4x smaller loop body for the instruction cache at the price of operands passing
+// through local memory; measured against the inlined form before choosing.
+#ifndef B2_TREE_FQ2_CALLS
+#define B2_TREE_FQ2_CALLS 0
+#endif
+#if defined(__CUDA_ARCH__) && B2_TREE_FQ2_CALLS
+static __device__ __noinline__ void tree_mul_wide12_call(uint32_t* t, const uint32_t* a, const uint32_t* b) { wide::mul_wide<12>(t, a, b); }
+static __device__ __noinline__ void tree_redc_call(uint32_t* r, const uint32_t* t) { wide::redc_wide<FqParams>(r, t); }
+B2_D Fq2 tree_mul(const Fq2& a, const Fq2& b) {
+    uint32_t t0[24], t1[24], t2[24], sa[12], sb[12];
+    tree_mul_wide12_call(t0, a.c0.v, b.c0.v);
+    tree_mul_wide12_call(t1, a.c1.v, b.c1.v);
+    wide::add_n<12>(sa, a.c0.v, a.c1.v);
+    wide::add_n<12>(sb, b.c0.v, b.c1.v);
+    tree_mul_wide12_call(t2, sa, sb);
+    wide::sub_wide(t2, t0);
+    wide::sub_wide(t2, t1);
+    const uint32_t neg = wide::sub_wide(t0, t1);
+    t0[12] = ptx::add_cc(t0[12], FqParams::mod_limb(0) & neg);
+#pragma unroll
+    for (int i = 1; i < 11; ++i) t0[12 + i] = ptx::addc_cc(t0[12 + i], FqParams::mod_limb(i) & neg);
+    t0[23] = ptx::addc(t0[23], FqParams::mod_limb(11) & neg);
+    Fq2 r;
+    tree_redc_call(r.c0.v, t0);
+    tree_redc_call(r.c1.v, t2);
+    return r;
+}
+B2_D Fq2 tree_sqr(const Fq2& a) { return a.sqr_inline(); }
+#elif B2_TREE_INLINE_FQ2
 B2_HD Fq2 tree_mul(const Fq2& a, const Fq2& b) { return wide::fq2_mul_lazy<false>(a, b); }
 B2_HD Fq2 tree_sqr(const Fq2& a) { return a.sqr_inline(); }
 #else
