@@ -20,6 +20,13 @@ B2_HD int msm_signed_digit(const uint32_t* s, int w, int c) {
     return (int)u + (int)msm_bit(s, lo - 1) - (int)(msm_bit(s, lo + c - 1) << c);
 }
 
+// Bit-decomposition tail of the bucket reduction (msm_reduce_bits_kernel): the j-th index, in increasing order, whose
+// bit b is set -- the high part of j moves up by one position and bit b is forced on.
+B2_HD uint32_t msm_bits_index(uint32_t j, int b) {
+    const uint32_t low = (1u << b) - 1u;
+    return ((j >> b) << (b + 1)) | (1u << b) | (j & low);
+}
+
 // chunk partition of the 2^(c-1) buckets of a window for the running-sum reduction
 B2_HD uint32_t msm_reduce_chunks(int c) {
     uint32_t B = 1u << (c - 1), T = B / 8;

@@ -414,10 +414,8 @@ msm_reduce_bits_kernel(const Xyzz<F>* __restrict__ a_in, const Xyzz<F>* __restri
     if (b == NB) {
         for (uint32_t t = threadIdx.x; t < count; t += blockDim.x) { Xyzz<F> v = src[t]; xyzz_add_call(&acc, &v); }
     } else {
-        // j-th index with bit b set: the high part of j moves up by one position, bit b is forced on
-        const uint32_t low = (1u << b) - 1u;
         for (uint32_t j = threadIdx.x;; j += blockDim.x) {
-            const uint32_t t = ((j >> b) << (b + 1)) | (1u << b) | (j & low);
+            const uint32_t t = msm_bits_index(j, b);                       // j-th index with bit b set
             if (t >= count) break;                       // t grows with j
             Xyzz<F> v = src[t]; xyzz_add_call(&acc, &v);
         }

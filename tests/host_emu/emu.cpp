@@ -173,6 +173,29 @@ int emu_msm_digits(const uint8_t* scalar, int c, int* out) {
     for (int w = 0; w < W; ++w) out[w] = msm_signed_digit(s, w, c);
     return W;
 }
+// Tail of the bucket reduction by bit decomposition (msm_reduce_bits_kernel + msm_reduce_bits_final_kernel), sequentially:
+// V = sum_t a_t + 2^log_s sum_t t r_t = sum_t a_t + 2^log_s sum_b 2^b S_b,  S_b = sum of the r_t whose index has bit b set,
+// enumerated with the kernel's own msm_bits_index.  a, r: count affine G1 points each (ABI bytes); out: affine.
+int emu_reduce_bits_g1(const uint8_t* a, const uint8_t* r, uint32_t count, int log_s, uint8_t* out) {
+    int NB = 0;
+    while ((1u << NB) < count) ++NB;
+    Xyzz<Fq> total = Xyzz<Fq>::identity();
+    for (int b = NB - 1; b >= 0; --b) {                       // Horner over the bits: total = 2 total + S_b
+        total = total.dbl();
+        Xyzz<Fq> S = Xyzz<Fq>::identity();
+        for (uint32_t j = 0;; ++j) {
+            const uint32_t t = msm_bits_index(j, b);
+            if (t >= count) break;
+            Affine<Fq> p; if (!load(p, r + 96 * (size_t)t)) return -2;
+            S.add_mixed(p);
+        }
+        total.add(S);
+    }
+    for (int k = 0; k < log_s; ++k) total = total.dbl();
+    for (uint32_t t = 0; t < count; ++t) { Affine<Fq> p; if (!load(p, a + 96 * (size_t)t)) return -2; total.add_mixed(p); }
+    store(total.to_affine(), out);
+    return NB;
+}
 // The MSM pipeline of msm_impl.cuh restated sequentially with the same bucket layout,
 // segment split, chunked running sum (+ chunk-offset lift) and Horner tail.
 int emu_msm_g1(const uint8_t* bases, const uint8_t* scalars, size_t n, int c, uint32_t S, uint8_t* out) {

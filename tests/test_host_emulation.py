@@ -289,6 +289,35 @@ def test_msm_tree_levels_vs_oracle(emu2, oracle, group, n, c, K, K2, levels):
     assert np.array_equal(out, want)
 
 
+
+
+@pytest.mark.parametrize("count,log_s", [(1, 0), (2, 3), (7, 0), (64, 3), (100, 6), (513, 3)])
+def test_reduce_bits_tail_vs_oracle(emu2, oracle, count, log_s):
+    """The bit-decomposition tail of the bucket reduction (msm_bits_index enumeration + Horner over the bits) equals
+    sum_t a_t + 2^log_s sum_t t r_t computed by the oracle's multiexp."""
+    rng = np.random.Generator(np.random.PCG64(count * 31 + log_s))
+    a = oracle.g1_gen_mul(codec.random_fr(count, rng))
+    r = oracle.g1_gen_mul(codec.random_fr(count, rng))
+    if count > 3:
+        r[2] = 0; a[1] = 0                                   # identities among the items
+    # the enumeration itself: every index with bit b set, once, in increasing order
+    for b in range(max(1, (count - 1).bit_length())):
+        got = []
+        j = 0
+        while True:
+            t = ((j >> b) << (b + 1)) | (1 << b) | (j & ((1 << b) - 1))
+            if t >= count:
+                break
+            got.append(t); j += 1
+        assert got == [t for t in range(count) if (t >> b) & 1]
+    out = np.zeros(96, dtype=np.uint8)
+    nb = emu2.emu_reduce_bits_g1(_p(a), _p(r), C.c_uint32(count), log_s, _p(out))
+    assert nb == (0 if count <= 1 else (count - 1).bit_length())
+    scal = codec.fr_from_ints([1] * count + [(t << log_s) % codec.R_MOD for t in range(count)])
+    want = oracle.msm_g1(np.concatenate([a, r]), scal)
+    assert np.array_equal(out, np.asarray(want).reshape(-1)[:96])
+
+
 @pytest.mark.parametrize("field", ["fr", "fq"])
 def test_inverse_by_gcd_equals_fermat(emu, oracle, field):
     """Fp::inv_gcd (binary extended Euclid on the limbs, used for the one inversion per tree level) against the
