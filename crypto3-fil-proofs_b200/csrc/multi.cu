@@ -7,8 +7,8 @@
 // partition order.  These entry points give that caller every GPU of the box without torch.distributed:
 //   * b2g16_prove_batch_multi: partitions -> devices.  Full waves run one partition per device at a time (independent
 //     units, the key replicated, no data-path exchange; device i takes a contiguous run of partitions through
-//     b2g16_prove_batch, which overlaps the next witness upload with the current proof); the last partial wave splits the devices into groups and each group
-//     proves ONE partition in latency mode (every member reduces its slice of the five queries,
+//     b2g16_prove_batch, which overlaps the next witness upload with the current proof); the last partial wave splits
+//     the devices into groups and each group proves ONE partition in latency mode (every member reduces its slice of the five queries,
 //     b2g16_prove_partial; 576 bytes per member come back to the host and are assembled), so no device idles.
 //   * b2g16_prove_multi: one proof over all devices in latency mode (a WindowPoSt / WinningPoSt proof is one partition).
 // Built on the single-device entry points of include/b2g16.h only; python/b2g16/dist.py is the same schedule for the

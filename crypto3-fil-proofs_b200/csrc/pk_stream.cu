@@ -5,8 +5,9 @@
 // read path core/parameter_cache.hpp:125-129).  On a GPU the key must be resident, so the equivalent is:
 //   b2g16_params_map   : the offset / count table of the five queries and the vk block (what build_mapped_parameters
 //                        computes), from the length prefixes alone -- no point is read;
-//   b2g16_pk_load_file : streams each query through a ring of pinned host buffers (the read of chunk k+1 -- positioned reads split over four threads -- overlaps the
-//                        cudaMemcpyAsync + conversion kernel of chunk k) and converts ON THE DEVICE: big-endian file
+//   b2g16_pk_load_file : streams each query through a ring of pinned host buffers (the read of chunk k+1 -- positioned
+//                        reads split over four threads -- overlaps the cudaMemcpyAsync + conversion kernel of chunk k)
+//                        and converts ON THE DEVICE: big-endian file
 //                        coordinates -> little-endian limbs -> Montgomery form, range + curve checks, G2 coefficient
 //                        order, infinity flag.  Density-filtered a / b_g1 / b_g2 queries (bellman's layout) are expanded
 //                        on the device into the dense layout through a position table, so neither the filtered nor the
